@@ -1,0 +1,144 @@
+// integrate.cuh — K7: fused kick-drift integrate + physical re-order, and the AoS<->SoA /
+// original-order helpers of the C ABI.
+#pragma once
+#include "common.cuh"
+
+namespace nb {
+
+struct BodyArrays {
+  float *x, *y, *vx, *vy;
+  uint32_t *m, *id; // integer mass; original body index of the slot
+};
+
+// Reference src/main.rs:419-423:  v += a*dt;  x += v*dt  (separate mul and add: Rust does not
+// contract).  Body j of the tree order is read from its old storage slot and written to slot j of
+// the other buffer, so the next step's storage is already Morton-ordered (coalesced writes, near-
+// coalesced gathers).  Acceleration follows the body (identity semantics; see DESIGN.md on the
+// reference's index-mismatch bug).
+__global__ void __launch_bounds__(256) integrate_resort_kernel(const uint32_t *__restrict__ order,
+                                                               const float2 *__restrict__ sacc, BodyArrays in,
+                                                               BodyArrays out, uint32_t jfirst, uint32_t jcount,
+                                                               float dt) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= jcount) return;
+  const uint32_t j = jfirst + k;
+  const uint32_t s = order[j];
+  const float2 a = sacc[j];
+  const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
+  const float vy = __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
+  out.vx[j] = vx;
+  out.vy[j] = vy;
+  out.x[j] = __fadd_rn(in.x[s], __fmul_rn(vx, dt));
+  out.y[j] = __fadd_rn(in.y[s], __fmul_rn(vy, dt));
+  out.m[j] = in.m[s];
+  out.id[j] = in.id[s];
+}
+
+// Permute only mass/id for tree positions outside [jfirst, jfirst+jcount) (multi-GPU: the
+// other ranks' bodies arrive by all-gather, mass and id are replicated and permuted locally).
+__global__ void __launch_bounds__(256) permute_mid_kernel(const uint32_t *__restrict__ order, BodyArrays in,
+                                                          BodyArrays out, uint32_t n, uint32_t jfirst,
+                                                          uint32_t jcount) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n || (j >= jfirst && j < jfirst + jcount)) return;
+  const uint32_t s = order[j];
+  out.m[j] = in.m[s];
+  out.id[j] = in.id[s];
+}
+
+__global__ void __launch_bounds__(256) aos_to_soa_kernel(const float *__restrict__ aos /*6 words per body*/,
+                                                         BodyArrays b, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float2 p = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i);
+  const float2 v = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i + 2);
+  const uint2 w = *reinterpret_cast<const uint2 *>(aos + 6 * (size_t)i + 4);
+  b.x[i] = p.x; b.y[i] = p.y; b.vx[i] = v.x; b.vy[i] = v.y; b.m[i] = w.x; b.id[i] = i;
+}
+
+// Slot order -> ORIGINAL body order AoS.
+__global__ void __launch_bounds__(256) soa_to_aos_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const size_t o = 6 * (size_t)b.id[s];
+  *reinterpret_cast<float2 *>(aos + o) = make_float2(b.x[s], b.y[s]);
+  *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(b.vx[s], b.vy[s]);
+  *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
+}
+
+__global__ void __launch_bounds__(256) set_identity_kernel(uint32_t *id, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) id[i] = i;
+}
+
+// Slot order -> original order, one u32/f32 word per body.
+__global__ void __launch_bounds__(256) unpermute_word_kernel(const uint32_t *__restrict__ src,
+                                                             const uint32_t *__restrict__ id, uint32_t n,
+                                                             uint32_t *__restrict__ dst) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) dst[id[s]] = src[s];
+}
+__global__ void __launch_bounds__(256) unpermute_key_kernel(const unsigned long long *__restrict__ src,
+                                                            const uint32_t *__restrict__ id, uint32_t n,
+                                                            unsigned long long *__restrict__ dst) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) dst[id[s]] = src[s];
+}
+
+// Tree-order accelerations -> ORIGINAL body order (the `acceleration` Vec of main.rs:406-416).
+__global__ void __launch_bounds__(256) accel_to_original_kernel(const float2 *__restrict__ sacc,
+                                                                const uint32_t *__restrict__ order,
+                                                                const uint32_t *__restrict__ id, uint32_t n,
+                                                                float *__restrict__ ax, float *__restrict__ ay) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const uint32_t o = id[order[j]];
+  const float2 a = sacc[j];
+  ax[o] = a.x;
+  ay[o] = a.y;
+}
+
+// tree position -> original id
+__global__ void __launch_bounds__(256) order_to_original_kernel(const uint32_t *__restrict__ order,
+                                                                const uint32_t *__restrict__ id, uint32_t n,
+                                                                uint32_t *__restrict__ out) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) out[j] = id[order[j]];
+}
+
+// original id -> slot
+__global__ void __launch_bounds__(256) slot_of_id_kernel(const uint32_t *__restrict__ id, uint32_t n,
+                                                         uint32_t *__restrict__ slot_of) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) slot_of[id[s]] = s;
+}
+
+// `draw` (reference src/main.rs:41-72) as two passes over a headless RGBA8 frame:
+//   pass 1 per body: heavy bodies (weight > 10) mark their pixel; light bodies count hits and
+//          record the LAST body (largest original index) hitting the pixel — the reference's
+//          sequential loop leaves the colour of the last light body drawn before alpha hit 0xff.
+//   pass 2 per pixel: compose exactly what the sequential loop would have left.
+// The sequential semantics depend on array order only through (a) the last light writer while
+// alpha != 0xff and (b) heavy bodies overriding; see nbody_b200.cu for the composition rule.
+struct DrawScratch {
+  uint32_t *hits;   // light-body hits per pixel
+  uint32_t *last;   // max original id + 1 of a light body on the pixel
+  uint32_t *heavy;  // max original id + 1 of a heavy body on the pixel
+};
+
+__global__ void __launch_bounds__(256) draw_splat_kernel(BodyArrays b, uint32_t n, uint32_t render_h, float world_h,
+                                                         uint32_t cell, DrawScratch d) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const float px = b.x[s], py = b.y[s];
+  if (!(py < world_h && px < world_h && py >= 0.f && px >= 0.f)) return; // within_bounds, main.rs:223-226
+  const uint32_t pix = ((uint32_t)py / cell) * render_h + ((uint32_t)px / cell);
+  const uint32_t oid = b.id[s] + 1u;
+  if (b.m[s] > 10u) atomicMax(&d.heavy[pix], oid);
+  else {
+    atomicAdd(&d.hits[pix], 1u);
+    atomicMax(&d.last[pix], oid);
+  }
+}
+
+} // namespace nb

@@ -1,0 +1,813 @@
+// nbody_b200.cu — context + C ABI (include/nbody_b200.h) of the B200-native Barnes-Hut step.
+//
+// Host-side mirror of the reference's `World` (src/main.rs:37-39) and `World::update`
+// (src/main.rs:388-425): build tree -> up-sweep -> traverse -> integrate, three timed phases
+// accumulated into a Counting-like struct.  All state lives in HBM; a step is enqueued on one
+// stream with no host synchronisation inside it.  There is no CPU fallback.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h> // types only; libnccl is dlopen'ed in nb_comm_init
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/nbody_b200.h"
+#include "common.cuh"
+#include "direct.cuh"
+#include "integrate.cuh"
+#include "morton.cuh"
+#include "radix_sort.cuh"
+#include "scan.cuh"
+#include "traverse.cuh"
+#include "tree_build.cuh"
+
+using namespace nb;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct NcclApi {
+  void *lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool load(std::string &err) {
+    if (lib) return true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names) {
+      lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (lib) break;
+    }
+    if (!lib) {
+      err = std::string("cannot dlopen libnccl: ") + dlerror();
+      return false;
+    }
+#define NB_SYM(field, name)                                      \
+  *(void **)(&field) = dlsym(lib, name);                         \
+  if (!field) {                                                  \
+    err = std::string("libnccl lacks symbol ") + name;           \
+    return false;                                                \
+  }
+    NB_SYM(GetUniqueId, "ncclGetUniqueId");
+    NB_SYM(CommInitRank, "ncclCommInitRank");
+    NB_SYM(CommDestroy, "ncclCommDestroy");
+    NB_SYM(AllGather, "ncclAllGather");
+    NB_SYM(GroupStart, "ncclGroupStart");
+    NB_SYM(GroupEnd, "ncclGroupEnd");
+    NB_SYM(GetErrorString, "ncclGetErrorString");
+#undef NB_SYM
+    return true;
+  }
+};
+NcclApi g_nccl;
+
+} // namespace
+
+struct nb_ctx {
+  nb_config cfg{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint32_t n = 0;       // bodies set
+  uint32_t n_alloc = 0; // array capacity (padded)
+  int leaf_cap = 8;
+  bool quad = true;
+
+  BodyArrays body[2]{};
+  int cur = 0; // body[cur] holds the current state (slot order)
+  unsigned long long *keys[2]{};
+  uint32_t *vals[2]{};
+  int sorted_in = 0; // keys[sorted_in] / vals[sorted_in] hold the sorted keys / tree order
+  uint8_t *leafdepth = nullptr;
+  uint32_t *nstart = nullptr; // per-body node counts, scanned in place to pre-order bases
+  SortScratch sort{};
+  TreeArrays T{};
+  float4 *sbody = nullptr; // bodies in tree order: (x, y, mass f32, mass bits)
+  float2 *sacc = nullptr;  // accelerations in tree order
+  float4 *bounds_partial = nullptr;
+  Meta *meta = nullptr; // device
+  Meta *h_meta = nullptr; // pinned host mirror
+  float *aos = nullptr;  // 6 words per body staging
+  void *flush_buf = nullptr;
+  size_t flush_bytes = 0;
+  bool tree_valid = false;
+  unsigned long long seen_interactions = 0, seen_tests = 0;
+
+  std::vector<cudaEvent_t> ev; // 5 per timed step, drained in batches
+  size_t ev_used = 0;
+
+  // multi-GPU
+  int rank = 0, n_ranks = 1;
+  ncclComm_t comm = nullptr;
+
+  std::string err;
+};
+
+namespace {
+
+int fail(nb_ctx *c, int code, const std::string &msg) {
+  if (c) c->err = msg;
+  else g_create_error = msg;
+  return code;
+}
+
+#define NB_CUDA(c, call)                                                                           \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return fail(c, NB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));            \
+  } while (0)
+
+template <class Tp> cudaError_t dmalloc(Tp **p, size_t count) { return cudaMalloc((void **)p, count * sizeof(Tp)); }
+
+inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+
+int alloc_bodies(nb_ctx *c, BodyArrays &b, size_t n) {
+  NB_CUDA(c, dmalloc(&b.x, n));
+  NB_CUDA(c, dmalloc(&b.y, n));
+  NB_CUDA(c, dmalloc(&b.vx, n));
+  NB_CUDA(c, dmalloc(&b.vy, n));
+  NB_CUDA(c, dmalloc(&b.m, n));
+  NB_CUDA(c, dmalloc(&b.id, n));
+  return NB_OK;
+}
+void free_bodies(BodyArrays &b) {
+  cudaFree(b.x); cudaFree(b.y); cudaFree(b.vx); cudaFree(b.vy); cudaFree(b.m); cudaFree(b.id);
+  b = BodyArrays{};
+}
+
+// owned range of tree positions for this rank
+void owned_range(const nb_ctx *c, uint32_t &first, uint32_t &count) {
+  if (c->n_ranks <= 1) {
+    first = 0;
+    count = c->n;
+    return;
+  }
+  uint32_t per = cdiv(c->n, (uint32_t)c->n_ranks);
+  first = std::min(c->n, per * (uint32_t)c->rank);
+  count = std::min(per, c->n - first);
+}
+
+// ---- one build: morton -> sort -> topology -> up-sweep (BVHTree::from + calculate_gravity,
+// bvh_tree.rs:57-158 / QuadTree::insert + calculate_gravity, quad_tree.rs:153-270) --------------
+int enqueue_build(nb_ctx *c) {
+  const uint32_t n = c->n;
+  cudaStream_t st = c->stream;
+  BodyArrays &b = c->body[c->cur];
+  if (n == 0) return NB_OK;
+  if (!c->quad && c->cfg.domain_auto) {
+    const int np = kSMs * 4;
+    bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
+    bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
+  }
+  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
+  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st);
+  c->sorted_in = which;
+  const unsigned long long *skeys = c->keys[which];
+  uint32_t *order = c->vals[which];
+  tree_prepare_kernel<<<1, 32, 0, st>>>(skeys, n, c->quad ? 1 : 0, c->meta);
+  const uint32_t gb = cdiv(n, 256);
+  if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
+  else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
+  exclusive_scan_u32(c->nstart, c->nstart, &c->meta->n_in, n, c->sort.bsum, &c->meta->n_nodes, st);
+  if (c->quad) tree_emit_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
+  else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
+  tree_link_kernel<<<kSMs * 8, 256, 0, st>>>(c->meta, c->T);
+  tree_leaf_gather_kernel<<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  if (c->quad) tree_upsweep_kernel<false><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, c->sbody);
+  else tree_upsweep_kernel<true><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, c->sbody);
+  NB_CUDA(c, cudaGetLastError());
+  c->tree_valid = true;
+  return NB_OK;
+}
+
+// World::bvh_sum_gravity over the par_iter (main.rs:349-386, 406-416) for tree positions
+// [first, first+count).
+int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
+  if (count == 0) return NB_OK;
+  const uint32_t blocks = cdiv(cdiv(count, 32), 8);
+  if (c->cfg.force_mode == NB_FORCE_EXACT)
+    traverse_kernel<true><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.cm, c->T.link, c->meta, c->sbody, c->sacc,
+                                                         c->cfg.theta, first, count);
+  else
+    traverse_kernel<false><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.cm, c->T.link, c->meta, c->sbody, c->sacc,
+                                                          c->cfg.theta, first, count);
+  NB_CUDA(c, cudaGetLastError());
+  return NB_OK;
+}
+
+int nccl_fail(nb_ctx *c, ncclResult_t r, const char *what) {
+  return fail(c, NB_ERR_NCCL, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
+}
+
+// integrate (main.rs:419-423) fused with the physical re-order; multi-GPU: all-gather slices.
+int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
+  const uint32_t n = c->n;
+  if (n == 0) return NB_OK;
+  uint32_t first, count;
+  owned_range(c, first, count);
+  BodyArrays &in = c->body[c->cur], &out = c->body[c->cur ^ 1];
+  const uint32_t *order = c->vals[c->sorted_in];
+  if (count)
+    integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt);
+  if (c->n_ranks > 1) {
+    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
+    if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
+    const size_t per = cdiv(n, (uint32_t)c->n_ranks);
+    ncclResult_t r;
+    if ((r = g_nccl.GroupStart()) != ncclSuccess) return nccl_fail(c, r, "ncclGroupStart");
+    float *arrs[4] = {out.x, out.y, out.vx, out.vy};
+    for (float *a : arrs) {
+      r = g_nccl.AllGather(a + per * (size_t)c->rank, a, per, ncclFloat32, c->comm, c->stream);
+      if (r != ncclSuccess) return nccl_fail(c, r, "ncclAllGather");
+    }
+    if ((r = g_nccl.GroupEnd()) != ncclSuccess) return nccl_fail(c, r, "ncclGroupEnd");
+  } else if (ev_after_integrate) {
+    NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
+  }
+  NB_CUDA(c, cudaGetLastError());
+  c->cur ^= 1;
+  c->tree_valid = false;
+  return NB_OK;
+}
+
+int sync_and_check(nb_ctx *c) {
+  NB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->meta, sizeof(Meta), cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->h_meta->error & 1u) {
+    return fail(c, NB_ERR_OVERFLOW,
+                "node pool too small: " + std::to_string(c->h_meta->n_nodes) + " nodes > capacity " +
+                    std::to_string(c->T.capacity));
+  }
+  return NB_OK;
+}
+
+void absorb_counters(nb_ctx *c, nb_counting *out) {
+  const unsigned long long ti = c->h_meta->interactions, tt = c->h_meta->node_tests;
+  if (out) {
+    out->interactions += ti - c->seen_interactions;
+    out->node_tests += tt - c->seen_tests;
+  }
+  c->seen_interactions = ti;
+  c->seen_tests = tt;
+}
+
+cudaEvent_t next_event(nb_ctx *c) {
+  if (c->ev_used == c->ev.size()) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+    c->ev.push_back(e);
+  }
+  return c->ev[c->ev_used++];
+}
+
+// events are recorded 5 per step: start, after build, after traverse, after integrate, end
+void drain_events(nb_ctx *c, nb_counting *out) {
+  const size_t steps = c->ev_used / 5;
+  for (size_t s = 0; s < steps; ++s) {
+    cudaEvent_t *e = &c->ev[5 * s];
+    float ms = 0.f;
+    if (out) {
+      if (cudaEventElapsedTime(&ms, e[0], e[1]) == cudaSuccess) out->build_s += ms * 1e-3;
+      if (cudaEventElapsedTime(&ms, e[1], e[2]) == cudaSuccess) out->traverse_s += ms * 1e-3;
+      if (cudaEventElapsedTime(&ms, e[2], e[3]) == cudaSuccess) out->integrate_s += ms * 1e-3;
+      if (cudaEventElapsedTime(&ms, e[3], e[4]) == cudaSuccess) out->exchange_s += ms * 1e-3;
+    }
+  }
+  if (out && steps) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[5 * (steps - 1) + 4]) == cudaSuccess) out->total_s += ms * 1e-3;
+  }
+  c->ev_used = 0;
+}
+
+int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
+  int rc;
+  for (uint32_t s = 0; s < n_steps; ++s) {
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, e3 = nullptr, e4 = nullptr;
+    if (out) {
+      e0 = next_event(c); e1 = next_event(c); e2 = next_event(c); e3 = next_event(c); e4 = next_event(c);
+      if (!e4) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+      NB_CUDA(c, cudaEventRecord(e0, c->stream));
+    }
+    if ((rc = enqueue_build(c)) != NB_OK) return rc;
+    if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
+    uint32_t first, count;
+    owned_range(c, first, count);
+    if ((rc = enqueue_traverse(c, first, count)) != NB_OK) return rc;
+    if (out) NB_CUDA(c, cudaEventRecord(e2, c->stream));
+    if ((rc = enqueue_integrate(c, dt, e3)) != NB_OK) return rc;
+    if (out) NB_CUDA(c, cudaEventRecord(e4, c->stream));
+    if (out && c->ev_used >= 5 * 256) { // bound the number of live events
+      if ((rc = sync_and_check(c)) != NB_OK) return rc;
+      drain_events(c, out);
+    }
+  }
+  if ((rc = sync_and_check(c)) != NB_OK) return rc;
+  drain_events(c, out);
+  absorb_counters(c, out);
+  if (out) out->steps += n_steps;
+  return NB_OK;
+}
+
+__global__ void draw_compose_kernel(DrawScratch d, const uint32_t *__restrict__ slot_of, BodyArrays b,
+                                    uint32_t npix, uint8_t *__restrict__ frame) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= npix) return;
+  uchar4 px = make_uchar4(0, 0, 0, 0); // frame zeroed first, main.rs:43
+  if (d.heavy[p]) {
+    px = make_uchar4(0x00, 0xff, 0x00, 0xff); // main.rs:55-59
+  } else if (d.hits[p]) {
+    const uint32_t s = slot_of[d.last[p] - 1u];
+    // main.rs:61-63: 0x10 + (((|vx|+|vy|)*10.0) as u8).min(0xef); `as u8` saturates, NaN -> 0
+    const float sp = __fmul_rn(__fadd_rn(fabsf(b.vx[s]), fabsf(b.vy[s])), 10.0f);
+    uint32_t q = (sp != sp) ? 0u : (sp <= 0.f ? 0u : (sp >= 255.f ? 255u : (uint32_t)sp));
+    q = q < 0xefu ? q : 0xefu;
+    const uint32_t vel = 0x10u + q;
+    const uint32_t hits = d.hits[p];
+    const uint32_t alpha = hits >= 25u ? 250u : hits * 10u; // += 10 while <= 240, main.rs:67-69
+    px = make_uchar4(0xff, (unsigned char)(0xffu - vel), (unsigned char)(0xffu - vel), (unsigned char)alpha);
+  }
+  reinterpret_cast<uchar4 *>(frame)[p] = px;
+}
+
+} // namespace
+
+// ======================================================================================
+// C ABI
+// ======================================================================================
+extern "C" {
+
+int nb_abi_version(void) { return NB_ABI_VERSION; }
+
+void nb_default_config(nb_config *cfg, uint64_t n_max) {
+  std::memset(cfg, 0, sizeof(*cfg));
+  cfg->n_max = n_max;
+  cfg->theta = 50.0f;   // THETA, main.rs:35
+  cfg->dt = 0.1f;       // STEP_SIZE, main.rs:34
+  cfg->tree_kind = NB_TREE_QUAD;
+  cfg->leaf_cap = 0;
+  cfg->domain_x0 = 0.f;
+  cfg->domain_y0 = 0.f;
+  cfg->domain_h = 100000.f; // HEIGHT, main.rs:31
+  cfg->force_mode = NB_FORCE_FAST;
+}
+
+const char *nb_last_error(const nb_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+void nb_destroy(nb_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+  free_bodies(c->body[0]);
+  free_bodies(c->body[1]);
+  for (int i = 0; i < 2; ++i) { cudaFree(c->keys[i]); cudaFree(c->vals[i]); }
+  cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.table); cudaFree(c->sort.bsum);
+  cudaFree(c->T.box); cudaFree(c->T.cm); cudaFree(c->T.link); cudaFree(c->T.mass); cudaFree(c->T.depth);
+  cudaFree(c->T.bmax); cudaFree(c->T.arrive);
+  cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
+  cudaFree(c->flush_buf);
+  if (c->h_meta) cudaFreeHost(c->h_meta);
+  for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+nb_ctx *nb_create(const nb_config *cfg) {
+  if (!cfg || cfg->n_max == 0 || cfg->n_max > 0x7fff0000ull) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: n_max must be in [1, 2^31)");
+    return nullptr;
+  }
+  if (cfg->tree_kind != NB_TREE_QUAD && cfg->tree_kind != NB_TREE_LBVH) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: unknown tree_kind");
+    return nullptr;
+  }
+  if (cfg->leaf_cap < 0 || cfg->leaf_cap > 64) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: leaf_cap must be in [0, 64]");
+    return nullptr;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    fail(nullptr, NB_ERR_CUDA,
+         std::string("nb_create: no CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
+             "); this library has no CPU fallback");
+    return nullptr;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: device ordinal out of range");
+    return nullptr;
+  }
+  nb_ctx *c = new nb_ctx();
+  c->cfg = *cfg;
+  c->device = cfg->device;
+  c->quad = cfg->tree_kind == NB_TREE_QUAD;
+  c->leaf_cap = cfg->leaf_cap ? cfg->leaf_cap : (c->quad ? 8 : 64);
+  if (c->cfg.domain_h <= 0.f) { c->cfg.domain_x0 = 0.f; c->cfg.domain_y0 = 0.f; c->cfg.domain_h = 100000.f; }
+  auto bail = [&](const char *what, cudaError_t err) -> nb_ctx * {
+    fail(nullptr, NB_ERR_CUDA, std::string("nb_create: ") + what + ": " + cudaGetErrorString(err));
+    nb_destroy(c);
+    return nullptr;
+  };
+#define NB_TRY(call)                                      \
+  if ((e = (call)) != cudaSuccess) return bail(#call, e)
+  NB_TRY(cudaSetDevice(c->device));
+  NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  const size_t na = ((size_t)cfg->n_max + 64 + 1023) / 1024 * 1024;
+  c->n_alloc = (uint32_t)na;
+  for (int i = 0; i < 2; ++i) {
+    if (alloc_bodies(c, c->body[i], na) != NB_OK) { g_create_error = c->err; nb_destroy(c); return nullptr; }
+    NB_TRY(dmalloc(&c->keys[i], na));
+    NB_TRY(dmalloc(&c->vals[i], na));
+  }
+  NB_TRY(dmalloc(&c->leafdepth, na));
+  NB_TRY(dmalloc(&c->nstart, na));
+  const size_t table = sort_table_entries((uint32_t)na);
+  NB_TRY(dmalloc(&c->sort.table, table));
+  NB_TRY(dmalloc(&c->sort.bsum, std::max<size_t>(table / kScanTile + 16, na / kScanTile + 16)));
+  const size_t ncap = 2 * na + 65536;
+  c->T.capacity = (uint32_t)std::min<size_t>(ncap, 0xfffffff0u);
+  NB_TRY(dmalloc(&c->T.box, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.cm, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.link, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.mass, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.depth, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.bmax, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.arrive, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->sbody, na));
+  NB_TRY(dmalloc(&c->sacc, na));
+  NB_TRY(dmalloc(&c->bounds_partial, (size_t)kSMs * 4));
+  NB_TRY(dmalloc(&c->meta, 1));
+  NB_TRY(dmalloc(&c->aos, 6 * na));
+  NB_TRY(cudaMallocHost((void **)&c->h_meta, sizeof(Meta)));
+  Meta m0{};
+  m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;
+  NB_TRY(cudaMemcpy(c->meta, &m0, sizeof(Meta), cudaMemcpyHostToDevice));
+  *c->h_meta = m0;
+#undef NB_TRY
+  return c;
+}
+
+int nb_set_params(nb_ctx *c, float theta, float dt, int32_t force_mode) {
+  if (!c) return NB_ERR_INVALID;
+  if (force_mode != NB_FORCE_EXACT && force_mode != NB_FORCE_FAST) return fail(c, NB_ERR_INVALID, "bad force_mode");
+  c->cfg.theta = theta;
+  c->cfg.dt = dt;
+  c->cfg.force_mode = force_mode;
+  return NB_OK;
+}
+
+void *nb_host_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+  return p;
+}
+void nb_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
+int nb_flush_l2(nb_ctx *c) {
+  if (!c) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (!c->flush_buf) {
+    c->flush_bytes = (size_t)256 << 20;
+    NB_CUDA(c, cudaMalloc(&c->flush_buf, c->flush_bytes));
+  }
+  NB_CUDA(c, cudaMemsetAsync(c->flush_buf, 0x5a, c->flush_bytes, c->stream));
+  return NB_OK;
+}
+
+int nb_set_bodies_aos(nb_ctx *c, const nb_particle *bodies, size_t n) {
+  if (!c || (!bodies && n)) return NB_ERR_INVALID;
+  if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_set_bodies: n > n_max");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->n = (uint32_t)n;
+  c->tree_valid = false;
+  if (n == 0) return NB_OK;
+  NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
+  aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NB_OK;
+}
+
+int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx, const float *vy,
+                      const uint32_t *w, size_t n) {
+  if (!c || (n && (!x || !y || !vx || !vy || !w))) return NB_ERR_INVALID;
+  if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_set_bodies: n > n_max");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->n = (uint32_t)n;
+  c->tree_valid = false;
+  if (n == 0) return NB_OK;
+  BodyArrays &b = c->body[c->cur];
+  NB_CUDA(c, cudaMemcpyAsync(b.x, x, n * 4, cudaMemcpyHostToDevice, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(b.y, y, n * 4, cudaMemcpyHostToDevice, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(b.vx, vx, n * 4, cudaMemcpyHostToDevice, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(b.vy, vy, n * 4, cudaMemcpyHostToDevice, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(b.m, w, n * 4, cudaMemcpyHostToDevice, c->stream));
+  set_identity_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(b.id, (uint32_t)n);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NB_OK;
+}
+
+int nb_get_bodies_aos(nb_ctx *c, nb_particle *bodies, size_t n) {
+  if (!c || (!bodies && n)) return NB_ERR_INVALID;
+  if (n < c->n) return fail(c, NB_ERR_CAPACITY, "nb_get_bodies: buffer smaller than body count");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (c->n == 0) return NB_OK;
+  soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaMemcpyAsync(bodies, c->aos, (size_t)c->n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NB_OK;
+}
+
+int nb_get_bodies_soa(nb_ctx *c, float *x, float *y, float *vx, float *vy, uint32_t *w, size_t n) {
+  if (!c) return NB_ERR_INVALID;
+  if (n < c->n) return fail(c, NB_ERR_CAPACITY, "nb_get_bodies: buffer smaller than body count");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (c->n == 0) return NB_OK;
+  BodyArrays &b = c->body[c->cur];
+  uint32_t *tmp = c->vals[c->sorted_in ^ 1]; // scratch (the tree order lives in vals[sorted_in])
+  const uint32_t *srcs[5] = {(const uint32_t *)b.x, (const uint32_t *)b.y, (const uint32_t *)b.vx,
+                             (const uint32_t *)b.vy, b.m};
+  void *dsts[5] = {x, y, vx, vy, w};
+  for (int k = 0; k < 5; ++k) {
+    if (!dsts[k]) continue;
+    unpermute_word_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(srcs[k], b.id, c->n, tmp);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(dsts[k], tmp, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return NB_OK;
+}
+
+int nb_step(nb_ctx *c, uint32_t n_steps, nb_counting *out) {
+  if (!c) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  return do_steps(c, n_steps, c->cfg.dt, out);
+}
+
+int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_counting *out) {
+  if (!c || (!bodies && n)) return NB_ERR_INVALID;
+  if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_world_update: n > n_max");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->n = (uint32_t)n;
+  c->tree_valid = false;
+  if (n == 0) return NB_OK;
+  NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
+  aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
+  int rc = do_steps(c, 1, delta, out);
+  if (rc != NB_OK) return rc;
+  soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaMemcpyAsync(bodies, c->aos, n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NB_OK;
+}
+
+int nb_build_tree(nb_ctx *c, nb_counting *out) {
+  if (!c) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (out) {
+    e0 = next_event(c); e1 = next_event(c);
+    if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+    NB_CUDA(c, cudaEventRecord(e0, c->stream));
+  }
+  int rc = enqueue_build(c);
+  if (rc != NB_OK) return rc;
+  if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
+  rc = sync_and_check(c);
+  if (out && rc == NB_OK) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
+  }
+  c->ev_used = 0;
+  return rc;
+}
+
+int nb_accel(nb_ctx *c, float *ax, float *ay, nb_counting *out) {
+  if (!c || !ax || !ay) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (c->n == 0) return NB_OK;
+  int rc;
+  cudaEvent_t e0 = next_event(c), e1 = next_event(c), e2 = next_event(c);
+  if (!e2) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+  NB_CUDA(c, cudaEventRecord(e0, c->stream));
+  if (!c->tree_valid && (rc = enqueue_build(c)) != NB_OK) return rc;
+  NB_CUDA(c, cudaEventRecord(e1, c->stream));
+  if ((rc = enqueue_traverse(c, 0, c->n)) != NB_OK) return rc;
+  NB_CUDA(c, cudaEventRecord(e2, c->stream));
+  // scratch: the unsorted ping-pong buffers are free once the tree is built
+  float *dax = reinterpret_cast<float *>(c->keys[c->sorted_in ^ 1]);
+  float *day = dax + c->n_alloc;
+  accel_to_original_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->sacc, c->vals[c->sorted_in],
+                                                                  c->body[c->cur].id, c->n, dax, day);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaMemcpyAsync(ax, dax, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(ay, day, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
+  if ((rc = sync_and_check(c)) != NB_OK) return rc;
+  if (out) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
+    if (cudaEventElapsedTime(&ms, e1, e2) == cudaSuccess) out->traverse_s += ms * 1e-3;
+  }
+  c->ev_used = 0;
+  absorb_counters(c, out);
+  return NB_OK;
+}
+
+int nb_accel_direct(nb_ctx *c, size_t first, size_t count, float *ax, float *ay, double *seconds) {
+  if (!c || !ax || !ay) return NB_ERR_INVALID;
+  if (first + count > c->n) return fail(c, NB_ERR_CAPACITY, "nb_accel_direct: target range exceeds body count");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (count == 0) return NB_OK;
+  const uint32_t n = c->n, nt = (uint32_t)count;
+  BodyArrays &b = c->body[c->cur];
+  uint32_t *slot_of = nullptr;
+  double *acc = nullptr;
+  float *dax = nullptr;
+  NB_CUDA(c, dmalloc(&slot_of, (size_t)n));
+  NB_CUDA(c, dmalloc(&acc, 2 * (size_t)nt));
+  NB_CUDA(c, dmalloc(&dax, 2 * (size_t)nt));
+  slot_of_id_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b.id, n, slot_of);
+  NB_CUDA(c, cudaMemsetAsync(acc, 0, 2 * (size_t)nt * sizeof(double), c->stream));
+  // split the sources so that the grid fills the machine even for few targets
+  const uint32_t tblocks = cdiv(nt, kDirectThreads);
+  uint32_t ychunks = std::max(1u, std::min(cdiv(n, 4096u), cdiv((uint32_t)kSMs * 8u, tblocks)));
+  ychunks = std::min(ychunks, 65535u);
+  uint32_t chunk = cdiv(cdiv(n, ychunks), kDirectThreads) * kDirectThreads;
+  ychunks = cdiv(n, chunk);
+  cudaEvent_t e0 = next_event(c), e1 = next_event(c);
+  if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+  NB_CUDA(c, cudaEventRecord(e0, c->stream));
+  dim3 grid(tblocks, ychunks);
+  if (c->cfg.force_mode == NB_FORCE_EXACT)
+    direct_kernel<true><<<grid, kDirectThreads, 0, c->stream>>>(b.x, b.y, b.m, n, slot_of + first, nt, acc, chunk);
+  else
+    direct_kernel<false><<<grid, kDirectThreads, 0, c->stream>>>(b.x, b.y, b.m, n, slot_of + first, nt, acc, chunk);
+  NB_CUDA(c, cudaEventRecord(e1, c->stream));
+  direct_finish_kernel<<<cdiv(nt, 256), 256, 0, c->stream>>>(acc, nt, dax, dax + nt);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaMemcpyAsync(ax, dax, (size_t)nt * 4, cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaMemcpyAsync(ay, dax + nt, (size_t)nt * 4, cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (seconds) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) *seconds = ms * 1e-3;
+  }
+  c->ev_used = 0;
+  cudaFree(slot_of); cudaFree(acc); cudaFree(dax);
+  return NB_OK;
+}
+
+int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {
+  if (!c || !info) return NB_ERR_INVALID;
+  if (!c->tree_valid) return fail(c, NB_ERR_INVALID, "no valid tree: call nb_build_tree or nb_accel first");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  int rc = sync_and_check(c);
+  if (rc != NB_OK) return rc;
+  std::memset(info, 0, sizeof(*info));
+  const Meta &m = *c->h_meta;
+  info->n_bodies = c->n;
+  info->n_in_tree = c->n ? m.n_in : 0;
+  info->n_nodes = c->n ? m.n_nodes : 0;
+  info->n_leaves = c->n ? m.n_leaves : 0;
+  info->max_depth = c->n ? m.max_depth : 0;
+  info->overflow_leaves = c->n ? m.overflow_leaves : 0;
+  info->root_x0 = m.x0; info->root_y0 = m.y0; info->root_h = m.h;
+  return NB_OK;
+}
+
+int nb_get_tree(nb_ctx *c, const nb_tree_view *v) {
+  if (!c || !v) return NB_ERR_INVALID;
+  nb_tree_info info;
+  int rc = nb_get_tree_info(c, &info);
+  if (rc != NB_OK) return rc;
+  const uint32_t n = c->n, nn = (uint32_t)info.n_nodes;
+  if (n == 0) return NB_OK;
+  BodyArrays &b = c->body[c->cur];
+  const int w = c->sorted_in;
+  if (v->keys) {
+    // recompute the slot-order keys into the free ping-pong buffer, then to original order
+    unsigned long long *tmp = nullptr;
+    NB_CUDA(c, dmalloc(&tmp, (size_t)n));
+    morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, c->stream>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[w ^ 1],
+                                                                  c->vals[w ^ 1]);
+    unpermute_key_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(c->keys[w ^ 1], b.id, n, tmp);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(v->keys, tmp, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(tmp);
+  }
+  if (v->order) {
+    uint32_t *tmp = c->vals[w ^ 1];
+    order_to_original_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(c->vals[w], b.id, n, tmp);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(v->order, tmp, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+    // bodies outside the root square: canonical (ascending id) order
+    std::sort(v->order + info.n_in_tree, v->order + n);
+  }
+  if (nn == 0) return NB_OK;
+  std::vector<uint4> link(nn);
+  std::vector<float4> box(nn), cm(nn);
+  NB_CUDA(c, cudaMemcpy(link.data(), c->T.link, (size_t)nn * sizeof(uint4), cudaMemcpyDeviceToHost));
+  NB_CUDA(c, cudaMemcpy(box.data(), c->T.box, (size_t)nn * sizeof(float4), cudaMemcpyDeviceToHost));
+  NB_CUDA(c, cudaMemcpy(cm.data(), c->T.cm, (size_t)nn * sizeof(float4), cudaMemcpyDeviceToHost));
+  if (v->node_depth) NB_CUDA(c, cudaMemcpy(v->node_depth, c->T.depth, (size_t)nn * 4, cudaMemcpyDeviceToHost));
+  if (v->node_mass) NB_CUDA(c, cudaMemcpy(v->node_mass, c->T.mass, (size_t)nn * 4, cudaMemcpyDeviceToHost));
+  for (uint32_t i = 0; i < nn; ++i) {
+    if (v->node_skip) v->node_skip[i] = link[i].x;
+    if (v->node_start) v->node_start[i] = link[i].y;
+    if (v->node_count) v->node_count[i] = link[i].z & ~kLeafBit;
+    if (v->node_leaf) v->node_leaf[i] = (link[i].z & kLeafBit) ? 1 : 0;
+    if (v->node_parent) v->node_parent[i] = link[i].w;
+    if (v->node_cogx) v->node_cogx[i] = cm[i].x;
+    if (v->node_cogy) v->node_cogy[i] = cm[i].y;
+    if (v->node_s2) v->node_s2[i] = cm[i].w;
+    if (v->node_x0) v->node_x0[i] = box[i].x;
+    if (v->node_y0) v->node_y0[i] = box[i].y;
+    if (v->node_x1) v->node_x1[i] = box[i].z;
+    if (v->node_y1) v->node_y1[i] = box[i].w;
+  }
+  return NB_OK;
+}
+
+int nb_draw(nb_ctx *c, uint8_t *frame, uint32_t render_h) {
+  if (!c || !frame || render_h == 0 || render_h > 16384) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  const uint32_t world_h = 100000u; // HEIGHT, main.rs:31
+  const uint32_t cell = world_h / render_h; // HEIGHT / RENDER_HEIGHT, integer, main.rs:51
+  if (cell == 0) return fail(c, NB_ERR_INVALID, "render_h larger than HEIGHT");
+  if ((world_h - 1) / cell >= render_h) return fail(c, NB_ERR_INVALID, "HEIGHT/render_h must cover the world");
+  const uint32_t npix = render_h * render_h, n = c->n;
+  DrawScratch d{};
+  uint32_t *buf = nullptr, *slot_of = nullptr;
+  uint8_t *dframe = nullptr;
+  NB_CUDA(c, dmalloc(&buf, 3 * (size_t)npix));
+  NB_CUDA(c, dmalloc(&slot_of, (size_t)std::max(n, 1u)));
+  NB_CUDA(c, dmalloc(&dframe, 4 * (size_t)npix));
+  d.hits = buf; d.last = buf + npix; d.heavy = buf + 2 * (size_t)npix;
+  NB_CUDA(c, cudaMemsetAsync(buf, 0, 3 * (size_t)npix * 4, c->stream));
+  BodyArrays &b = c->body[c->cur];
+  if (n) {
+    slot_of_id_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b.id, n, slot_of);
+    draw_splat_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b, n, render_h, (float)world_h, cell, d);
+  }
+  draw_compose_kernel<<<cdiv(npix, 256), 256, 0, c->stream>>>(d, slot_of, b, npix, dframe);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaMemcpyAsync(frame, dframe, 4 * (size_t)npix, cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  cudaFree(buf); cudaFree(slot_of); cudaFree(dframe);
+  return NB_OK;
+}
+
+// ---- multi-GPU -------------------------------------------------------------------------------
+int nb_comm_unique_id(uint8_t id[NB_UNIQUE_ID_BYTES]) {
+  std::string err;
+  if (!g_nccl.load(err)) return fail(nullptr, NB_ERR_NCCL, err);
+  ncclUniqueId u;
+  ncclResult_t r = g_nccl.GetUniqueId(&u);
+  if (r != ncclSuccess) return fail(nullptr, NB_ERR_NCCL, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+  static_assert(sizeof(ncclUniqueId) <= NB_UNIQUE_ID_BYTES, "unique id size");
+  std::memset(id, 0, NB_UNIQUE_ID_BYTES);
+  std::memcpy(id, &u, sizeof(u));
+  return NB_OK;
+}
+
+int nb_comm_init(nb_ctx *c, int rank, int n_ranks, const uint8_t id[NB_UNIQUE_ID_BYTES]) {
+  if (!c || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return NB_ERR_INVALID;
+  if (n_ranks == 1) { c->rank = 0; c->n_ranks = 1; return NB_OK; }
+  std::string err;
+  if (!g_nccl.load(err)) return fail(c, NB_ERR_NCCL, err);
+  NB_CUDA(c, cudaSetDevice(c->device));
+  ncclUniqueId u;
+  std::memcpy(&u, id, sizeof(u));
+  ncclResult_t r = g_nccl.CommInitRank(&c->comm, n_ranks, u, rank);
+  if (r != ncclSuccess) return nccl_fail(c, r, "ncclCommInitRank");
+  c->rank = rank;
+  c->n_ranks = n_ranks;
+  return NB_OK;
+}
+
+int nb_comm_owned_range(nb_ctx *c, uint64_t *first, uint64_t *count) {
+  if (!c || !first || !count) return NB_ERR_INVALID;
+  uint32_t f, n;
+  owned_range(c, f, n);
+  *first = f;
+  *count = n;
+  return NB_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,403 @@
+// tree_build.cuh — K3/K4: fully parallel tree construction from sorted Morton keys
+// (common-prefix queries + binary searches, in the manner of Karras 2012) and the atomic
+// bottom-up mass / centre-of-gravity / bounds up-sweep.
+//
+// One formulation serves both trees (template BPL = key bits per tree level):
+//   BPL=2, uncompressed  -> region quadtree of reference src/quad_tree.rs (fresh-build topology:
+//                           a cell is internal iff it holds > cap bodies, single-child chains kept)
+//   BPL=1, compressed    -> binary radix tree (LBVH) with bucket leaves <= cap, the B200 variant of
+//                           reference src/bvh_tree.rs (tight AABBs, same up-sweep / traversal)
+//
+// Definitions over the sorted keys k[0..n_in):
+//   cpl(i,j)   common prefix length of k[i], k[j] in levels
+//   L(i)       leaf depth of body i = min(D, 1 + (cap-th largest cpl(i,j) over j != i))
+//              -> the depth-L(i) cell around i holds <= cap bodies, the depth-(L(i)-1) cell > cap
+//   c(i)       cpl(i-1,i)  (c(0) = -1)
+//   body i starts the nodes at depths c(i)+1 .. L(i) (it is the first body of those cells); the
+//   deepest is a leaf.  Ordering nodes by (first body, depth) IS depth-first pre-order, so an
+//   exclusive scan of the per-body node counts yields the pre-order index of every node, and
+//   skip(node) = index of the first node starting at the node's end body.
+#pragma once
+#include "common.cuh"
+#include "scan.cuh"
+
+namespace nb {
+
+struct TreeArrays {
+  float4 *box;        // (x0, y0, x1, y1): the four f32 values Rectangle::contains compares with
+  float4 *cm;         // (cog.x, cog.y, mass as f32, s2 = max(w,h)^2)
+  uint4 *link;        // (skip, first body, count | leaf<<31, parent)
+  uint32_t *mass;     // u32 wrapping mass
+  int32_t *depth;
+  float2 *bmax;       // LBVH: max corner (for the bounds union)
+  uint32_t *arrive;   // up-sweep arrival counters (bodies arrived per internal node)
+  uint32_t capacity;  // node pool size
+};
+
+constexpr uint32_t kLeafBit = 0x80000000u;
+
+__global__ void tree_prepare_kernel(const unsigned long long *__restrict__ skeys, uint32_t n, int quad_mode,
+                                    Meta *meta) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  uint32_t n_in = n;
+  if (quad_mode) { // first sorted position holding kKeyOut
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (skeys[mid] < kKeyOut) lo = mid + 1;
+      else hi = mid;
+    }
+    n_in = lo;
+  }
+  meta->n = n;
+  meta->n_in = n_in;
+  meta->n_nodes = 0;
+  meta->n_leaves = 0;
+  meta->max_depth = 0;
+  meta->overflow_leaves = 0;
+}
+
+// smallest j in (i, hi) whose depth-d prefix differs from k[i]'s; hi if none.  Gallop + bisect.
+template <int BPL>
+__device__ __forceinline__ uint32_t find_end(const unsigned long long *__restrict__ skeys, uint32_t i,
+                                             unsigned long long ki, int d, uint32_t hi) {
+  if (d <= 0) return hi;
+  const int sh = kKeyBits - d * BPL;
+  const unsigned long long p = ki >> sh;
+  uint32_t lo = i + 1, step = 1, probe = lo;
+  while (probe < hi && (skeys[probe] >> sh) == p) {
+    lo = probe + 1;
+    probe = lo + step;
+    step <<= 1;
+  }
+  if (probe < hi) hi = probe;
+  while (lo < hi) {
+    uint32_t mid = (lo + hi) >> 1;
+    if ((skeys[mid] >> sh) == p) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// L(i): merge outward over the two monotone neighbour sequences, cap steps.
+template <int BPL>
+__device__ __forceinline__ int leaf_depth_of(const unsigned long long *__restrict__ skeys, uint32_t i,
+                                             unsigned long long ki, uint32_t n_in, int cap) {
+  constexpr int D = kKeyBits / BPL;
+  int l = (int)i - 1, r = (int)i + 1;
+  int cl = (l >= 0) ? cpl<BPL>(skeys[l], ki) : -1;
+  int cr = (r < (int)n_in) ? cpl<BPL>(skeys[r], ki) : -1;
+  int c = -1;
+  for (int s = 0; s < cap; ++s) {
+    if (cl < 0 && cr < 0) { c = -1; break; }
+    if (cl >= cr) {
+      c = cl;
+      --l;
+      cl = (l >= 0) ? cpl<BPL>(skeys[l], ki) : -1;
+    } else {
+      c = cr;
+      ++r;
+      cr = (r < (int)n_in) ? cpl<BPL>(skeys[r], ki) : -1;
+    }
+  }
+  int L = c + 1;
+  return L > D ? D : L;
+}
+
+// Pass 1: L(i) and the number of nodes body i starts.
+template <int BPL, bool COMPRESS>
+__global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
+                                                         int cap, uint8_t *__restrict__ leafdepth,
+                                                         uint32_t *__restrict__ nstart) {
+  const uint32_t n_in = meta->n_in;
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t cnt = 0, isleaf = 0, over = 0;
+  int L = 0, statdepth = 0;
+  if (i < n_in) {
+    const unsigned long long ki = skeys[i];
+    L = leaf_depth_of<BPL>(skeys, i, ki, n_in, cap);
+    const int c = (i > 0) ? cpl<BPL>(skeys[i - 1], ki) : -1;
+    leafdepth[i] = (uint8_t)L;
+    statdepth = L;
+    if (c < L) {
+      isleaf = 1;
+      if (!COMPRESS) {
+        cnt = (uint32_t)(L - c);
+        if (L == kKeyBits / BPL) { // depth cap: is the leaf over-full?
+          uint32_t e = find_end<BPL>(skeys, i, ki, L, n_in);
+          over = (e - i > (uint32_t)cap);
+        }
+      } else {
+        int d = c + 1;
+        uint32_t e = find_end<BPL>(skeys, i, ki, d, n_in);
+        for (;;) {
+          int delta = cpl<BPL>(ki, skeys[e - 1]);
+          ++cnt;
+          if (delta >= L) {
+            over = (e - i > (uint32_t)cap);
+            statdepth = delta; // recorded leaf depth = tight common prefix of the bucket
+            break;
+          }
+          d = delta + 1;
+          e = find_end<BPL>(skeys, i, ki, d, e);
+        }
+      }
+    }
+    nstart[i] = cnt;
+  }
+  // block-aggregated statistics
+  uint32_t leaves = __syncthreads_count(isleaf);
+  uint32_t overs = __syncthreads_count(over);
+  __shared__ int smax;
+  if (threadIdx.x == 0) smax = 0;
+  __syncthreads();
+  if (isleaf) atomicMax(&smax, statdepth);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (leaves) atomicAdd(&meta->n_leaves, leaves);
+    if (overs) atomicAdd(&meta->overflow_leaves, overs);
+    if (smax) atomicMax(&meta->max_depth, (uint32_t)smax);
+  }
+}
+
+// Pass 2 (after the scan of nstart into base, total in meta->n_nodes): write the nodes.
+template <int BPL, bool COMPRESS>
+__global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
+                                                        const uint8_t *__restrict__ leafdepth,
+                                                        const uint32_t *__restrict__ base, TreeArrays T) {
+  const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
+  if (n_nodes > T.capacity) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
+    return;
+  }
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_in) return;
+  const unsigned long long ki = skeys[i];
+  const int L = leafdepth[i];
+  const int c = (i > 0) ? cpl<BPL>(skeys[i - 1], ki) : -1;
+  if (c >= L) return;
+  uint32_t idx = base[i];
+  if (!COMPRESS) {
+    // walk the reference's f32 midline chain (quad_tree.rs:172-194) down to depth L
+    float ox = meta->x0, oy = meta->y0, hh = meta->h;
+    uint32_t e = n_in;
+    for (int l = 0; l <= L; ++l) {
+      if (l > c) {
+        e = find_end<BPL>(skeys, i, ki, l, e);
+        const bool leaf = (l == L);
+        const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
+        T.depth[idx] = l;
+        T.link[idx] = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+        T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
+        T.cm[idx] = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
+        ++idx;
+      }
+      if (l < L) {
+        hh = __fmul_rn(hh, 0.5f);
+        const float mx = __fadd_rn(ox, hh), my = __fadd_rn(oy, hh);
+        const uint32_t dg = (uint32_t)(ki >> (kKeyBits - 2 * (l + 1))) & 3u;
+        ox = (dg & 1u) ? mx : ox;
+        oy = (dg & 2u) ? my : oy;
+      }
+    }
+  } else {
+    int d = c + 1;
+    uint32_t e = find_end<BPL>(skeys, i, ki, d, n_in);
+    for (;;) {
+      const int delta = cpl<BPL>(ki, skeys[e - 1]);
+      const bool leaf = (delta >= L);
+      const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
+      T.depth[idx] = delta;
+      T.link[idx] = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+      ++idx;
+      if (leaf) break;
+      d = delta + 1;
+      e = find_end<BPL>(skeys, i, ki, d, e);
+    }
+  }
+}
+
+// Parent links (from the parents' side) + reset of the arrival counters.
+__global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__ meta, TreeArrays T) {
+  if (meta->error) return;
+  const uint32_t n_nodes = meta->n_nodes;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n_nodes; p += gridDim.x * blockDim.x) {
+    T.arrive[p] = 0;
+    const uint4 l = T.link[p];
+    if (l.z & kLeafBit) continue;
+    for (uint32_t c = p + 1; c < l.x;) {
+      uint32_t *lc = reinterpret_cast<uint32_t *>(&T.link[c]);
+      lc[3] = p;
+      c = lc[0];
+    }
+  }
+}
+
+// Leaf fix-up + gather.  Inside every leaf the bodies are put in ascending ORIGINAL id order —
+// the order QuadTree::insert fills the slots (quad_tree.rs:163-164,221-224: insertion order, and
+// subdivide re-inserts in slot order), which fixes the f32 summation order of the leaf centre of
+// gravity (quad_tree.rs:236-240) and of the leaf interactions (main.rs:355-362).  Then the
+// tree-order body array (x, y, mass as f32, mass bits) is gathered.
+__global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__restrict__ meta, TreeArrays T,
+                                                               uint32_t *__restrict__ order,
+                                                               const float *__restrict__ x, const float *__restrict__ y,
+                                                               const uint32_t *__restrict__ m,
+                                                               const uint32_t *__restrict__ id,
+                                                               float4 *__restrict__ sbody) {
+  if (meta->error) return;
+  const uint32_t n_nodes = meta->n_nodes, n_in = meta->n_in, n = meta->n;
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  for (uint32_t p = tid; p < n_nodes; p += nth) {
+    const uint4 l = T.link[p];
+    if (!(l.z & kLeafBit)) continue;
+    const uint32_t s = l.y, k = l.z & ~kLeafBit;
+    if (k <= 64) {
+      uint32_t slot[64], bid[64];
+      for (uint32_t j = 0; j < k; ++j) {
+        slot[j] = order[s + j];
+        bid[j] = id[slot[j]];
+      }
+      for (uint32_t a = 1; a < k; ++a) { // insertion sort by id
+        uint32_t bs = slot[a], bi = bid[a];
+        int b = (int)a - 1;
+        while (b >= 0 && bid[b] > bi) {
+          slot[b + 1] = slot[b];
+          bid[b + 1] = bid[b];
+          --b;
+        }
+        slot[b + 1] = bs;
+        bid[b + 1] = bi;
+      }
+      for (uint32_t j = 0; j < k; ++j) {
+        const uint32_t sl = slot[j];
+        order[s + j] = sl;
+        const uint32_t mm = m[sl];
+        sbody[s + j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
+      }
+    } else { // over-full leaf at the depth cap: in-place insertion sort in global memory
+      for (uint32_t a = 1; a < k; ++a) {
+        uint32_t bs = order[s + a], bi = id[bs];
+        int b = (int)a - 1;
+        while (b >= 0 && id[order[s + b]] > bi) {
+          order[s + b + 1] = order[s + b];
+          --b;
+        }
+        order[s + b + 1] = bs;
+      }
+      for (uint32_t j = 0; j < k; ++j) {
+        const uint32_t sl = order[s + j];
+        const uint32_t mm = m[sl];
+        sbody[s + j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
+      }
+    }
+  }
+  // bodies outside the root square: targets only
+  for (uint32_t j = n_in + tid; j < n; j += nth) {
+    const uint32_t sl = order[j];
+    const uint32_t mm = m[sl];
+    sbody[j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
+  }
+}
+
+// K4: atomic bottom-up up-sweep.  One thread per leaf computes the leaf summary, then climbs:
+// at every parent it adds its subtree's body count to the parent's arrival counter; the thread
+// that completes the count owns the parent and folds the children IN CHILD ORDER (deterministic).
+//   leaf:     mass = wrapping u32 sum (bvh_tree.rs:123); cog = UNWEIGHTED mean of positions
+//             (bvh_tree.rs:104-107, quad_tree.rs:236-240)
+//   internal: mass = sum of child masses; cog = sum(child.cog * (child.mass as f32)) / (mass as f32)
+//             (quad_tree.rs:253-266 folds from (0,0); bvh_tree.rs:148-154 is a*m0 + b*m1)
+//   LBVH bounds: tight AABB with min seeded f32::MAX and max seeded 0 (bvh_tree.rs:42,59),
+//             size = max - min, s2 = max(w,h)^2 as main.rs:371 computes it.
+template <bool LBVH>
+__global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restrict__ meta, TreeArrays T,
+                                                           const float4 *__restrict__ sbody) {
+  if (meta->error) return;
+  const uint32_t n_nodes = meta->n_nodes;
+  for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < n_nodes; node += gridDim.x * blockDim.x) {
+    uint4 l = T.link[node];
+    if (!(l.z & kLeafBit)) continue;
+    const uint32_t s = l.y, k = l.z & ~kLeafBit;
+    float ax = 0.f, ay = 0.f;
+    uint32_t mass = 0;
+    float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
+    for (uint32_t j = 0; j < k; ++j) {
+      const float4 b = sbody[s + j];
+      ax = __fadd_rn(ax, b.x);
+      ay = __fadd_rn(ay, b.y);
+      mass += __float_as_uint(b.w);
+      if (LBVH) {
+        mnx = mnx < b.x ? mnx : b.x; // minps
+        mny = mny < b.y ? mny : b.y;
+        mxx = mxx > b.x ? mxx : b.x; // maxps
+        mxy = mxy > b.y ? mxy : b.y;
+      }
+    }
+    const float kf = (float)k;
+    float cx = __fdiv_rn(ax, kf), cy = __fdiv_rn(ay, kf);
+    float s2;
+    if (LBVH) {
+      const float w = __fsub_rn(mxx, mnx), h = __fsub_rn(mxy, mny);
+      const float tx = w > h ? w : h, ty = h > w ? h : w;
+      s2 = __fmul_rn(tx, ty);
+      T.box[node] = make_float4(mnx, mny, __fadd_rn(mnx, w), __fadd_rn(mny, h));
+      T.bmax[node] = make_float2(mxx, mxy);
+    } else {
+      s2 = T.cm[node].w;
+    }
+    T.cm[node] = make_float4(cx, cy, (float)mass, s2);
+    T.mass[node] = mass;
+
+    uint32_t cur = node, cur_count = k, parent = l.w;
+    while (parent != 0xffffffffu) {
+      __threadfence();
+      const uint32_t old = atomicAdd(&T.arrive[parent], cur_count);
+      const uint4 lp = T.link[parent];
+      const uint32_t total = lp.z & ~kLeafBit;
+      if (old + cur_count != total) break;
+      __threadfence();
+      uint32_t pm = 0;
+      float bx = 0.f, by = 0.f;
+      bool first = true;
+      mnx = 3.402823466e+38f; mny = 3.402823466e+38f; mxx = 0.f; mxy = 0.f;
+      for (uint32_t c = parent + 1; c < lp.x;) {
+        const uint32_t cm_u = __ldcg(&T.mass[c]);
+        const float4 ccm = __ldcg(&T.cm[c]);
+        const float mf = (float)cm_u;
+        const float tx = __fmul_rn(ccm.x, mf), ty = __fmul_rn(ccm.y, mf);
+        if (LBVH && first) { bx = tx; by = ty; }
+        else { bx = __fadd_rn(bx, tx); by = __fadd_rn(by, ty); }
+        first = false;
+        pm += cm_u;
+        if (LBVH) {
+          const float4 cb = __ldcg(&T.box[c]);
+          const float2 cmax = __ldcg(&T.bmax[c]);
+          mnx = mnx < cb.x ? mnx : cb.x;
+          mny = mny < cb.y ? mny : cb.y;
+          mxx = mxx > cmax.x ? mxx : cmax.x;
+          mxy = mxy > cmax.y ? mxy : cmax.y;
+        }
+        c = T.link[c].x;
+      }
+      const float pmf = (float)pm;
+      cx = __fdiv_rn(bx, pmf);
+      cy = __fdiv_rn(by, pmf);
+      if (LBVH) {
+        const float w = __fsub_rn(mxx, mnx), h = __fsub_rn(mxy, mny);
+        const float tx = w > h ? w : h, ty = h > w ? h : w;
+        s2 = __fmul_rn(tx, ty);
+        T.box[parent] = make_float4(mnx, mny, __fadd_rn(mnx, w), __fadd_rn(mny, h));
+        T.bmax[parent] = make_float2(mxx, mxy);
+      } else {
+        s2 = T.cm[parent].w;
+      }
+      T.cm[parent] = make_float4(cx, cy, pmf, s2);
+      T.mass[parent] = pm;
+      cur = parent;
+      cur_count = total;
+      parent = lp.w;
+    }
+    (void)cur;
+  }
+}
+
+} // namespace nb

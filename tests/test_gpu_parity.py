@@ -1,0 +1,247 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+inputs.  Bit-exact for Morton keys, sort order, topology, masses, centres of gravity, bounds and —
+in NB_FORCE_EXACT mode — forces and trajectories; stated normwise tolerance for NB_FORCE_FAST."""
+import numpy as np
+import pytest
+
+import nbody_simulation_b200 as nb
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+
+TREE_KEYS = ["keys", "order", "node_depth", "node_start", "node_count", "node_skip", "node_parent", "node_leaf",
+             "node_mass", "node_cogx", "node_cogy", "node_x0", "node_y0", "node_x1", "node_y1", "node_s2"]
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint8)
+
+
+def scene(name, n, seed=1):
+    kinds = {"default": nb.NB_SCENE_DEFAULT, "disc": nb.NB_SCENE_UNIFORM_DISC, "plummer": nb.NB_SCENE_PLUMMER,
+             "galaxy": nb.NB_SCENE_TWO_GALAXY}
+    return nb.generate_scene(kinds[name], seed, n)
+
+
+def assert_tree_equal(g, o, what):
+    assert g["info"].n_nodes == o["info"].n_nodes, what
+    assert g["info"].n_in_tree == o["info"].n_in_tree, what
+    assert g["info"].n_leaves == o["info"].n_leaves, what
+    assert g["info"].max_depth == o["info"].max_depth, what
+    assert g["info"].overflow_leaves == o["info"].overflow_leaves, what
+    for k in TREE_KEYS:
+        same = np.array_equal(bits(g[k]), bits(o[k]))
+        if not same:
+            bad = np.nonzero(g[k] != o[k])[0]
+            raise AssertionError(f"{what}: {k} differs at {len(bad)} of {len(g[k])} entries, first {bad[:5]}: "
+                                 f"gpu {g[k][bad[:5]]} oracle {o[k][bad[:5]]}")
+
+
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+@pytest.mark.parametrize("sc,n", [("disc", 100_000), ("default", 0), ("plummer", 150_000), ("galaxy", 120_001)])
+def test_tree_bitexact(tree, okind, sc, n):
+    p = scene(sc, n)
+    w = nb.World(len(p), tree=tree)
+    w.set_particles(p)
+    w.build_tree()
+    g = w.tree()
+    o = ob.Tree(okind, p["x"], p["y"], p["weight"]).export()
+    assert_tree_equal(g, o, f"{sc}/{tree}")
+    if tree == nb.NB_TREE_QUAD:  # and against the literal insert-built quad_tree.rs
+        lit = ob.Tree(ob.KIND_LITERAL_QUAD, p["x"], p["y"], p["weight"]).export()
+        lit["keys"] = o["keys"]
+        assert_tree_equal(g, lit, f"{sc}/literal quad_tree.rs")
+    w.close()
+
+
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+@pytest.mark.parametrize("theta", [0.5, 50.0])
+def test_accel_exact_is_bit_identical(tree, okind, theta):
+    p = scene("default", 0)
+    w = nb.World(len(p), theta=theta, tree=tree, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    c = nb.Counting()
+    ax, ay = w.accel(c)
+    T = ob.Tree(okind, p["x"], p["y"], p["weight"])
+    rx, ry, ni, nt, _ = T.accel(theta)
+    assert c.interactions == ni and c.node_tests == nt
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+def test_accel_fast_within_tolerance(tree, okind):
+    # tolerance: normwise ||da||2/||a||2 <= 1e-5 against the oracle on the SAME tree and theta
+    p = scene("disc", 200_000)
+    theta = 0.5
+    w = nb.World(len(p), theta=theta, tree=tree, force_mode=nb.NB_FORCE_FAST)
+    w.set_particles(p)
+    c = nb.Counting()
+    ax, ay = w.accel(c)
+    T = ob.Tree(okind, p["x"], p["y"], p["weight"])
+    rx, ry, ni, nt, _ = T.accel(theta)
+    assert c.interactions == ni and c.node_tests == nt  # same opening decisions
+    err = ob.normwise_err(ax, ay, rx, ry)
+    assert err <= 1e-5, err
+    w.close()
+
+
+def test_quad_literal_reference_forces():
+    # GPU exact forces == literal recursive quad_tree.rs walk (carried-over criterion) bit for bit
+    p = scene("disc", 60_000)
+    w = nb.World(len(p), theta=0.5, tree=nb.NB_TREE_QUAD, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    T = ob.Tree(ob.KIND_LITERAL_QUAD, p["x"], p["y"], p["weight"])
+    rx, ry, _, _, _ = T.accel(0.5, literal=True)
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+def test_trajectory_exact_is_bit_identical(tree, okind):
+    p = scene("default", 0)[:40_000].copy()
+    theta, dt, steps = 0.7, 0.1, 6
+    w = nb.World(len(p), theta=theta, dt=dt, tree=tree, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    c = nb.Counting()
+    w.step(steps, c)
+    ow = ob.OracleWorld(p)
+    oc = None
+    for _ in range(steps):
+        oc = ow.update(okind, dt, theta, counting=oc)
+    x, y, vx, vy, m = ow.get()
+    q = w.particles
+    assert c.interactions == oc.interactions and c.node_tests == oc.node_tests
+    for a, b in ((q["x"], x), (q["y"], y), (q["vx"], vx), (q["vy"], vy), (q["weight"], m)):
+        assert np.array_equal(bits(a), bits(b))
+    w.close()
+
+
+def test_world_update_host_roundtrip():
+    p = scene("disc", 50_000)
+    w = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    host = p.copy()
+    w.update_host(host, 0.1)
+    ow = ob.OracleWorld(p)
+    ow.update(ob.KIND_PIPE_QUAD, 0.1, 0.5)
+    x, y, vx, vy, _ = ow.get()
+    assert np.array_equal(bits(host["x"]), bits(x)) and np.array_equal(bits(host["vy"]), bits(vy))
+    w.close()
+
+
+def test_direct_sum_against_fp64():
+    p = scene("disc", 30_000)
+    w = nb.World(len(p), force_mode=nb.NB_FORCE_FAST)
+    w.set_particles(p)
+    first, count = 1000, 4096
+    ax, ay, _ = w.accel_direct(first, count)
+    rx, ry = ob.direct_f64(p["x"], p["y"], p["weight"], np.arange(first, first + count))
+    err = ob.normwise_err(ax, ay, rx, ry)
+    assert err <= 2e-6, err  # fp32 pair terms, fp32 256-tile partials, fp64 across tiles
+    w.close()
+
+
+def test_tree_force_vs_direct_sum():
+    # Barnes-Hut error level at theta = 0.5 (not a parity tolerance: documents the BH approximation)
+    p = scene("disc", 100_000)
+    w = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_FAST)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    dx, dy, _ = w.accel_direct(0, 8192)
+    err = ob.normwise_err(ax[:8192], ay[:8192], dx, dy)
+    assert err < 5e-3, err
+    w.close()
+
+
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+@pytest.mark.parametrize("n", [1, 2, 8, 9, 64, 65, 1000])
+def test_small_and_ragged(tree, okind, n):
+    p = scene("disc", n, seed=7)
+    w = nb.World(max(n, 1), theta=0.5, tree=tree, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    g = w.tree()
+    T = ob.Tree(okind, p["x"], p["y"], p["weight"])
+    assert_tree_equal(g, T.export(), f"n={n}")
+    rx, ry, _, _, _ = T.accel(0.5)
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+def test_out_of_domain_and_coincident_bodies():
+    rng = np.random.default_rng(3)
+    n = 5000
+    p = np.zeros(n, nb.PARTICLE_DTYPE)
+    p["x"] = rng.uniform(-2e4, 1.2e5, n).astype(np.float32)
+    p["y"] = rng.uniform(-2e4, 1.2e5, n).astype(np.float32)
+    p["weight"] = rng.integers(1, 50, n)
+    p["x"][100:140] = 777.25  # 40 coincident bodies: an over-full leaf at the depth cap
+    p["y"][100:140] = 4242.5
+    p["x"][200] = 0.0  # on the root's lower edge: inside (within_bounds uses >=)
+    p["x"][201] = 100000.0  # on the upper edge: outside
+    for tree, okind in ((nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)):
+        w = nb.World(n, theta=0.5, tree=tree, force_mode=nb.NB_FORCE_EXACT)
+        w.set_particles(p)
+        ax, ay = w.accel()
+        g = w.tree()
+        T = ob.Tree(okind, p["x"], p["y"], p["weight"])
+        o = T.export()
+        assert_tree_equal(g, o, f"edge/{tree}")
+        if tree == nb.NB_TREE_QUAD:
+            assert g["info"].n_in_tree < n and g["info"].overflow_leaves == 1
+        rx, ry, _, _, _ = T.accel(0.5)
+        assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+        w.close()
+
+
+def test_u32_mass_wraps_like_the_reference():
+    p = scene("disc", 3000, seed=5)
+    p["weight"] = 3_000_000_000  # sums wrap modulo 2^32 exactly like Rust release-mode u32 adds
+    w = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    w.build_tree()
+    g = w.tree()
+    o = ob.Tree(ob.KIND_PIPE_QUAD, p["x"], p["y"], p["weight"]).export()
+    assert_tree_equal(g, o, "wrap")
+    w.close()
+
+
+def test_lbvh_auto_domain():
+    p = scene("plummer", 50_000)
+    w = nb.World(len(p), theta=0.5, tree=nb.NB_TREE_LBVH, domain_auto=True, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    g = w.tree()
+    T = ob.Tree(ob.KIND_PIPE_LBVH, p["x"], p["y"], p["weight"], domain_auto=True)
+    assert_tree_equal(g, T.export(), "auto-domain")
+    rx, ry, _, _, _ = T.accel(0.5)
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+def test_draw_matches_sequential_reference():
+    p = scene("default", 0)
+    w = nb.World(len(p))
+    w.set_particles(p)
+    frame = w.draw()
+    # sequential restatement of draw() (src/main.rs:41-72)
+    H, R = 100000, 1250
+    ref = np.zeros((R * R, 4), np.uint8)
+    for q in p:
+        x, y = q["x"], q["y"]
+        if not (y < H and x < H and y >= 0 and x >= 0):
+            continue
+        off = (int(y) // (H // R)) * R + (int(x) // (H // R))
+        if q["weight"] > 10:
+            ref[off] = (0, 255, 0, 255)
+        elif ref[off, 3] != 255:
+            sp = np.float32(np.float32(abs(q["vx"]) + abs(q["vy"])) * np.float32(10.0))
+            vel = 0x10 + min(int(min(max(sp, 0), 255)), 0xef)
+            ref[off, 0] = 255
+            ref[off, 1] = 255 - vel
+            ref[off, 2] = 255 - vel
+            if ref[off, 3] <= 240:
+                ref[off, 3] += 10
+    assert np.array_equal(frame.reshape(-1, 4), ref)
+    w.close()
