@@ -47,6 +47,7 @@ class Counting:
     steps = property(lambda s: s.c.steps)
     interactions = property(lambda s: s.c.interactions)
     node_tests = property(lambda s: s.c.node_tests)
+    launches = property(lambda s: s.c.launches)
 
     def __repr__(self):  # the reference prints `{:?}` once per second (main.rs:152)
         return (f"Counting {{ build_bvh: {self.build_bvh}, sum_gravity: {self.sum_gravity}, "
@@ -157,6 +158,9 @@ class World:
         if force_mode is not None:
             self.cfg.force_mode = int(force_mode)
         self._ck(self._L.nb_set_params(self._ctx, self.cfg.theta, self.cfg.dt, self.cfg.force_mode))
+
+    def set_counting(self, enabled):
+        self._ck(self._L.nb_set_counting(self._ctx, 1 if enabled else 0))
 
     # ---- the step ------------------------------------------------------------------------
     def update(self, delta=None, counter=None):

@@ -51,7 +51,8 @@ class NbCounting(C.Structure):
         ("steps", C.c_uint64),
         ("interactions", C.c_uint64),
         ("node_tests", C.c_uint64),
-        ("reserved", C.c_uint64 * 4),
+        ("launches", C.c_uint64),
+        ("reserved", C.c_uint64 * 3),
     ]
 
 
@@ -121,6 +122,7 @@ def load(path=LIB_PATH):
         "nb_destroy": (None, [vp]),
         "nb_last_error": (C.c_char_p, [vp]),
         "nb_set_params": (C.c_int, [vp, C.c_float, C.c_float, C.c_int32]),
+        "nb_set_counting": (C.c_int, [vp, C.c_int]),
         "nb_set_bodies_aos": (C.c_int, [vp, vp, C.c_size_t]),
         "nb_set_bodies_soa": (C.c_int, [vp, f32p, f32p, f32p, f32p, u32p, C.c_size_t]),
         "nb_get_bodies_aos": (C.c_int, [vp, vp, C.c_size_t]),

@@ -6,6 +6,9 @@
 namespace nb {
 
 constexpr int kSMs = 148;                 // B200
+
+// Kernel launches issued by this library on the calling thread (reported in nb_counting).
+static thread_local unsigned long long g_launches = 0;
 constexpr int kKeyBits = 48;              // 24 quadtree levels x 2 bits (y bit above x bit)
 constexpr int kQuadLevels = 24;
 constexpr unsigned long long kKeyOut = 1ull << 48; // body outside the root square (quadtree mode)
@@ -21,7 +24,7 @@ struct Meta {
   uint32_t max_depth;
   uint32_t overflow_leaves;
   uint32_t error;           // bit 0: node pool too small
-  uint32_t _padu;
+  uint32_t cog_outside;     // != 0: some internal node's centre of gravity lies outside its box
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)
 };

@@ -98,6 +98,7 @@ struct nb_ctx {
   void *flush_buf = nullptr;
   size_t flush_bytes = 0;
   bool tree_valid = false;
+  bool counting = true; // interaction / opening-test counters in the traversal
   unsigned long long seen_interactions = 0, seen_tests = 0;
 
   std::vector<cudaEvent_t> ev; // 5 per timed step, drained in batches
@@ -164,9 +165,11 @@ int enqueue_build(nb_ctx *c) {
   if (n == 0) return NB_OK;
   if (!c->quad && c->cfg.domain_auto) {
     const int np = kSMs * 4;
+    g_launches += 2;
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
+  g_launches += 7; // morton, prepare, count, emit, link, leaf-gather, up-sweep (+ sort and scan, counted there)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st);
   c->sorted_in = which;
@@ -193,12 +196,16 @@ int enqueue_build(nb_ctx *c) {
 int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   if (count == 0) return NB_OK;
   const uint32_t blocks = cdiv(cdiv(count, 32), 8);
-  if (c->cfg.force_mode == NB_FORCE_EXACT)
-    traverse_kernel<true><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.cm, c->T.link, c->meta, c->sbody, c->sacc,
-                                                         c->cfg.theta, first, count);
-  else
-    traverse_kernel<false><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.cm, c->T.link, c->meta, c->sbody, c->sacc,
-                                                          c->cfg.theta, first, count);
+  g_launches += 1;
+#define NB_TRAVERSE(EX, CNT)                                                                                  \
+  traverse_kernel<EX, CNT><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,          \
+                                                          c->cfg.theta, first, count)
+  const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
+  if (ex && c->counting) NB_TRAVERSE(true, true);
+  else if (ex) NB_TRAVERSE(true, false);
+  else if (c->counting) NB_TRAVERSE(false, true);
+  else NB_TRAVERSE(false, false);
+#undef NB_TRAVERSE
   NB_CUDA(c, cudaGetLastError());
   return NB_OK;
 }
@@ -215,6 +222,7 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   owned_range(c, first, count);
   BodyArrays &in = c->body[c->cur], &out = c->body[c->cur ^ 1];
   const uint32_t *order = c->vals[c->sorted_in];
+  g_launches += (count ? 1 : 0) + (c->n_ranks > 1 ? 1 : 0);
   if (count)
     integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt);
   if (c->n_ranks > 1) {
@@ -290,6 +298,7 @@ void drain_events(nb_ctx *c, nb_counting *out) {
 
 int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
   int rc;
+  const unsigned long long launches0 = g_launches;
   for (uint32_t s = 0; s < n_steps; ++s) {
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, e3 = nullptr, e4 = nullptr;
     if (out) {
@@ -313,7 +322,10 @@ int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
   if ((rc = sync_and_check(c)) != NB_OK) return rc;
   drain_events(c, out);
   absorb_counters(c, out);
-  if (out) out->steps += n_steps;
+  if (out) {
+    out->steps += n_steps;
+    out->launches += g_launches - launches0;
+  }
   return NB_OK;
 }
 
@@ -371,7 +383,7 @@ void nb_destroy(nb_ctx *c) {
   free_bodies(c->body[1]);
   for (int i = 0; i < 2; ++i) { cudaFree(c->keys[i]); cudaFree(c->vals[i]); }
   cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.table); cudaFree(c->sort.bsum);
-  cudaFree(c->T.box); cudaFree(c->T.cm); cudaFree(c->T.link); cudaFree(c->T.mass); cudaFree(c->T.depth);
+  cudaFree(c->T.box); cudaFree(c->T.node); cudaFree(c->T.mass); cudaFree(c->T.depth);
   cudaFree(c->T.bmax); cudaFree(c->T.arrive);
   cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
   cudaFree(c->flush_buf);
@@ -436,8 +448,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   const size_t ncap = 2 * na + 65536;
   c->T.capacity = (uint32_t)std::min<size_t>(ncap, 0xfffffff0u);
   NB_TRY(dmalloc(&c->T.box, (size_t)c->T.capacity));
-  NB_TRY(dmalloc(&c->T.cm, (size_t)c->T.capacity));
-  NB_TRY(dmalloc(&c->T.link, (size_t)c->T.capacity));
+  NB_TRY(dmalloc(&c->T.node, 2 * (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.mass, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.depth, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.bmax, (size_t)c->T.capacity));
@@ -462,6 +473,12 @@ int nb_set_params(nb_ctx *c, float theta, float dt, int32_t force_mode) {
   c->cfg.theta = theta;
   c->cfg.dt = dt;
   c->cfg.force_mode = force_mode;
+  return NB_OK;
+}
+
+int nb_set_counting(nb_ctx *c, int enabled) {
+  if (!c) return NB_ERR_INVALID;
+  c->counting = enabled != 0;
   return NB_OK;
 }
 
@@ -721,10 +738,13 @@ int nb_get_tree(nb_ctx *c, const nb_tree_view *v) {
   }
   if (nn == 0) return NB_OK;
   std::vector<uint4> link(nn);
-  std::vector<float4> box(nn), cm(nn);
-  NB_CUDA(c, cudaMemcpy(link.data(), c->T.link, (size_t)nn * sizeof(uint4), cudaMemcpyDeviceToHost));
+  std::vector<float4> box(nn), cm(nn), inter(2 * (size_t)nn);
+  NB_CUDA(c, cudaMemcpy(inter.data(), c->T.node, 2 * (size_t)nn * sizeof(float4), cudaMemcpyDeviceToHost));
+  for (uint32_t i = 0; i < nn; ++i) {
+    cm[i] = inter[2 * (size_t)i];
+    std::memcpy(&link[i], &inter[2 * (size_t)i + 1], sizeof(uint4));
+  }
   NB_CUDA(c, cudaMemcpy(box.data(), c->T.box, (size_t)nn * sizeof(float4), cudaMemcpyDeviceToHost));
-  NB_CUDA(c, cudaMemcpy(cm.data(), c->T.cm, (size_t)nn * sizeof(float4), cudaMemcpyDeviceToHost));
   if (v->node_depth) NB_CUDA(c, cudaMemcpy(v->node_depth, c->T.depth, (size_t)nn * 4, cudaMemcpyDeviceToHost));
   if (v->node_mass) NB_CUDA(c, cudaMemcpy(v->node_mass, c->T.mass, (size_t)nn * 4, cudaMemcpyDeviceToHost));
   for (uint32_t i = 0; i < nn; ++i) {

@@ -119,6 +119,7 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
   int shift = 0;
   while (shift < bits) {
     int rb = (bits - shift == 9) ? 9 : 8;
+    g_launches += 2;
     if (rb == 8) {
       sort_hist_kernel<8><<<nblocks, kSortThreads, 0, st>>>(kin, n, shift, nblocks, sc.table);
       exclusive_scan_u32(sc.table, sc.table, nullptr, 256u * nblocks, sc.bsum, nullptr, st);

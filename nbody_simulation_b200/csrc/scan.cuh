@@ -113,6 +113,7 @@ inline void exclusive_scan_u32(const uint32_t *in, uint32_t *out, const uint32_t
                                uint32_t *bsum_scratch, uint32_t *total_out, cudaStream_t st) {
   uint32_t nb = (n_max + kScanTile - 1) / kScanTile;
   if (nb == 0) nb = 1;
+  g_launches += 3;
   scan_reduce_kernel<<<nb, kScanThreads, 0, st>>>(in, n_ptr, n_max, bsum_scratch);
   scan_bsum_kernel<<<1, 1024, 0, st>>>(bsum_scratch, nb, total_out);
   scan_apply_kernel<<<nb, kScanThreads, 0, st>>>(in, out, n_ptr, n_max, bsum_scratch);

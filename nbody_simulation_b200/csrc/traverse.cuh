@@ -8,15 +8,47 @@
 // A's subtree.  Each lane therefore evaluates exactly the node/leaf sequence its private
 // recursive walk would, in the same order, so with EXACT arithmetic the result is bit-identical
 // to the scalar recursion.
+//
+// Instruction economy (the kernel is issue-bound, see profiles/):
+//  * the opening test and the accepted interaction share diff and |diff|^2: dist2(p, cog)
+//    (main.rs:229-232) squares p - cog, calculate_gravity (main.rs:236,245) squares cog - p — the
+//    same bits — so an accepted node costs 7 more instructions, not 11;
+//  * FAST mode with theta^2 <= 1/2 drops Rectangle::contains: a body strictly inside the box and a
+//    centre of gravity inside the box are at most sqrt(w^2+h^2) <= sqrt(2)*s apart, so
+//    s^2 < d^2*theta^2 cannot hold; the up-sweep flags the (pathological, u32-wrapped-mass) case
+//    of a centre of gravity outside its box and the kernel then keeps the test;
+//  * the interaction / opening-test counters are compiled out unless asked for.
 #pragma once
 #include "common.cuh"
 #include "tree_build.cuh"
 
 namespace nb {
 
+// main.rs:235-253 with diff = (dx, dy) and d2 = dx*dx + dy*dy already computed.
 template <bool EXACT>
-__global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict__ box, const float4 *__restrict__ cm,
-                                                       const uint4 *__restrict__ link, Meta *meta,
+__device__ __forceinline__ void force_from_diff(float dx, float dy, float d2, float m, float &ax, float &ay) {
+  if (EXACT) {
+    const float sum = __fadd_rn(fabsf(dx), fabsf(dy));
+    const uint32_t b = __float_as_uint(sum);
+    if (b - 0x00800000u < 0x7f000000u) { // sum.is_normal()
+      const float d = d2 < 0.001f ? 0.001f : d2;
+      const float den = __fmul_rn(sum, d);
+      ax = __fadd_rn(ax, __fdiv_rn(__fmul_rn(dx, m), den));
+      ay = __fadd_rn(ay, __fdiv_rn(__fmul_rn(dy, m), den));
+    }
+  } else {
+    const float sum = fabsf(dx) + fabsf(dy);
+    const float d = fmaxf(d2, 0.001f);
+    const float w = m * rcp_approx(fmaf(sum, d, 1e-20f));
+    ax = fmaf(dx, w, ax);
+    ay = fmaf(dy, w, ay);
+  }
+}
+
+template <bool EXACT, bool COUNT>
+__global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict__ box,
+                                                       const float4 *__restrict__ node /* [2i]=cm, [2i+1]=link */,
+                                                       Meta *meta,
                                                        const float4 *__restrict__ sbody, float2 *__restrict__ sacc,
                                                        float theta, uint32_t tfirst, uint32_t tcount) {
   if (meta->error) return;
@@ -32,45 +64,74 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
   uint32_t resume = valid ? 0u : 0xffffffffu; // lane is active at node `cur` iff cur >= resume
   uint32_t n_inter = 0, n_test = 0;
   const uint32_t n_nodes = meta->n_nodes;
+  const float theta2 = theta * theta;
+  // Rectangle::contains is needed unless provably implied (see header)
+  // (0.45 rather than 0.5 leaves slack for the 1% excursion the up-sweep tolerates)
+  const bool need_contains = EXACT || !(theta2 <= 0.45f) || meta->cog_outside != 0;
   uint32_t cur = 0;
   while (cur < n_nodes) {
-    const uint4 l = link[cur];
+    const float4 *np = node + 2 * (size_t)cur;
+    const float4 lf = np[1];
+    const uint4 l = make_uint4(__float_as_uint(lf.x), __float_as_uint(lf.y), __float_as_uint(lf.z), 0u);
     const bool active = cur >= resume;
     if (l.z & kLeafBit) {
-      const uint32_t s = l.y, k = l.z & ~kLeafBit;
-      for (uint32_t j = 0; j < k; ++j) {
-        const float4 b = sbody[s + j];
-        if (active) pair_force<EXACT>(px, py, b.x, b.y, b.z, ax, ay);
-      }
-      if (active) n_inter += k;
-      cur = cur + 1;
-    } else {
-      const float4 bx = box[cur];
-      const float4 c = cm[cur];
-      bool open = false;
+      const uint32_t k = l.z & ~kLeafBit;
+      const float4 *bp = sbody + l.y;
       if (active) {
-        ++n_test;
-        if (accept_node(px, py, bx, c.x, c.y, c.w, theta)) {
-          pair_force<EXACT>(px, py, c.x, c.y, c.z, ax, ay);
-          resume = l.x;
-          ++n_inter;
-        } else {
-          open = true;
+#pragma unroll 4
+        for (uint32_t j = 0; j < k; ++j) {
+          const float4 b = bp[j];
+          pair_force<EXACT>(px, py, b.x, b.y, b.z, ax, ay);
         }
       }
-      cur = __any_sync(0xffffffffu, open) ? cur + 1 : l.x;
+      if (COUNT && active) n_inter += k;
+      cur = cur + 1;
+    } else {
+      const float4 c = np[0];
+      float dx, dy, d2;
+      bool far;
+      if (EXACT) {
+        dx = __fsub_rn(c.x, px);
+        dy = __fsub_rn(c.y, py);
+        d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+        far = c.w < __fmul_rn(__fmul_rn(d2, theta), theta); // main.rs:371-372, left to right
+      } else {
+        dx = c.x - px;
+        dy = c.y - py;
+        d2 = fmaf(dy, dy, dx * dx);
+        far = c.w < d2 * theta2;
+      }
+      if (need_contains) {
+        const float4 bx = box[cur];
+        const bool contains = py > bx.y && px > bx.x && px < bx.z && py < bx.w;
+        far = far && !contains;
+      }
+      const bool acc = active && far;
+      if (__any_sync(0xffffffffu, acc)) {
+        if (acc) {
+          force_from_diff<EXACT>(dx, dy, d2, c.z, ax, ay);
+          resume = l.x;
+        }
+      }
+      if (COUNT) {
+        n_test += active ? 1u : 0u;
+        n_inter += acc ? 1u : 0u;
+      }
+      cur = __any_sync(0xffffffffu, active && !far) ? cur + 1 : l.x;
     }
   }
   if (valid) sacc[t] = make_float2(ax, ay);
-  unsigned long long wi = n_inter, wt = n_test;
+  if (COUNT) {
+    unsigned long long wi = n_inter, wt = n_test;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    wi += __shfl_xor_sync(0xffffffffu, wi, o);
-    wt += __shfl_xor_sync(0xffffffffu, wt, o);
-  }
-  if (lane == 0) {
-    atomicAdd(&meta->interactions, wi);
-    atomicAdd(&meta->node_tests, wt);
+    for (int o = 16; o > 0; o >>= 1) {
+      wi += __shfl_xor_sync(0xffffffffu, wi, o);
+      wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&meta->interactions, wi);
+      atomicAdd(&meta->node_tests, wt);
+    }
   }
 }
 

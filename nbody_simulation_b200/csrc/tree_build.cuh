@@ -25,8 +25,14 @@ namespace nb {
 
 struct TreeArrays {
   float4 *box;        // (x0, y0, x1, y1): the four f32 values Rectangle::contains compares with
-  float4 *cm;         // (cog.x, cog.y, mass as f32, s2 = max(w,h)^2)
-  uint4 *link;        // (skip, first body, count | leaf<<31, parent)
+  // The two records the traversal reads per node are interleaved (32 B per node, one address):
+  //   node[2i]   = cm   (cog.x, cog.y, mass as f32, s2 = max(w,h)^2)
+  //   node[2i+1] = link (skip, first body, count | leaf<<31, parent)
+  float4 *node;
+  __device__ __forceinline__ float4 &cm(uint32_t i) const { return node[2 * (size_t)i]; }
+  __device__ __forceinline__ uint4 &link(uint32_t i) const {
+    return reinterpret_cast<uint4 *>(node)[2 * (size_t)i + 1];
+  }
   uint32_t *mass;     // u32 wrapping mass
   int32_t *depth;
   float2 *bmax;       // LBVH: max corner (for the bounds union)
@@ -55,6 +61,7 @@ __global__ void tree_prepare_kernel(const unsigned long long *__restrict__ skeys
   meta->n_leaves = 0;
   meta->max_depth = 0;
   meta->overflow_leaves = 0;
+  meta->cog_outside = 0;
 }
 
 // smallest j in (i, hi) whose depth-d prefix differs from k[i]'s; hi if none.  Gallop + bisect.
@@ -187,9 +194,9 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
         const bool leaf = (l == L);
         const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
         T.depth[idx] = l;
-        T.link[idx] = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+        T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
         T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
-        T.cm[idx] = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
+        T.cm(idx) = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
         ++idx;
       }
       if (l < L) {
@@ -208,7 +215,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
       const bool leaf = (delta >= L);
       const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
       T.depth[idx] = delta;
-      T.link[idx] = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+      T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
       ++idx;
       if (leaf) break;
       d = delta + 1;
@@ -223,10 +230,10 @@ __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__
   const uint32_t n_nodes = meta->n_nodes;
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n_nodes; p += gridDim.x * blockDim.x) {
     T.arrive[p] = 0;
-    const uint4 l = T.link[p];
+    const uint4 l = T.link(p);
     if (l.z & kLeafBit) continue;
     for (uint32_t c = p + 1; c < l.x;) {
-      uint32_t *lc = reinterpret_cast<uint32_t *>(&T.link[c]);
+      uint32_t *lc = reinterpret_cast<uint32_t *>(&T.link(c));
       lc[3] = p;
       c = lc[0];
     }
@@ -248,7 +255,7 @@ __global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__res
   const uint32_t n_nodes = meta->n_nodes, n_in = meta->n_in, n = meta->n;
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
   for (uint32_t p = tid; p < n_nodes; p += nth) {
-    const uint4 l = T.link[p];
+    const uint4 l = T.link(p);
     if (!(l.z & kLeafBit)) continue;
     const uint32_t s = l.y, k = l.z & ~kLeafBit;
     if (k <= 64) {
@@ -309,12 +316,12 @@ __global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__res
 //   LBVH bounds: tight AABB with min seeded f32::MAX and max seeded 0 (bvh_tree.rs:42,59),
 //             size = max - min, s2 = max(w,h)^2 as main.rs:371 computes it.
 template <bool LBVH>
-__global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restrict__ meta, TreeArrays T,
+__global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ meta, TreeArrays T,
                                                            const float4 *__restrict__ sbody) {
   if (meta->error) return;
   const uint32_t n_nodes = meta->n_nodes;
   for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < n_nodes; node += gridDim.x * blockDim.x) {
-    uint4 l = T.link[node];
+    uint4 l = T.link(node);
     if (!(l.z & kLeafBit)) continue;
     const uint32_t s = l.y, k = l.z & ~kLeafBit;
     float ax = 0.f, ay = 0.f;
@@ -342,16 +349,16 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restric
       T.box[node] = make_float4(mnx, mny, __fadd_rn(mnx, w), __fadd_rn(mny, h));
       T.bmax[node] = make_float2(mxx, mxy);
     } else {
-      s2 = T.cm[node].w;
+      s2 = T.cm(node).w;
     }
-    T.cm[node] = make_float4(cx, cy, (float)mass, s2);
+    T.cm(node) = make_float4(cx, cy, (float)mass, s2);
     T.mass[node] = mass;
 
     uint32_t cur = node, cur_count = k, parent = l.w;
     while (parent != 0xffffffffu) {
       __threadfence();
       const uint32_t old = atomicAdd(&T.arrive[parent], cur_count);
-      const uint4 lp = T.link[parent];
+      const uint4 lp = T.link(parent);
       const uint32_t total = lp.z & ~kLeafBit;
       if (old + cur_count != total) break;
       __threadfence();
@@ -361,7 +368,7 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restric
       mnx = 3.402823466e+38f; mny = 3.402823466e+38f; mxx = 0.f; mxy = 0.f;
       for (uint32_t c = parent + 1; c < lp.x;) {
         const uint32_t cm_u = __ldcg(&T.mass[c]);
-        const float4 ccm = __ldcg(&T.cm[c]);
+        const float4 ccm = __ldcg(&T.cm(c));
         const float mf = (float)cm_u;
         const float tx = __fmul_rn(ccm.x, mf), ty = __fmul_rn(ccm.y, mf);
         if (LBVH && first) { bx = tx; by = ty; }
@@ -376,7 +383,7 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restric
           mxx = mxx > cmax.x ? mxx : cmax.x;
           mxy = mxy > cmax.y ? mxy : cmax.y;
         }
-        c = T.link[c].x;
+        c = T.link(c).x;
       }
       const float pmf = (float)pm;
       cx = __fdiv_rn(bx, pmf);
@@ -388,10 +395,15 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(const Meta *__restric
         T.box[parent] = make_float4(mnx, mny, __fadd_rn(mnx, w), __fadd_rn(mny, h));
         T.bmax[parent] = make_float2(mxx, mxy);
       } else {
-        s2 = T.cm[parent].w;
+        s2 = T.cm(parent).w;
       }
-      T.cm[parent] = make_float4(cx, cy, pmf, s2);
+      T.cm(parent) = make_float4(cx, cy, pmf, s2);
       T.mass[parent] = pm;
+      { // the traversal may drop Rectangle::contains only if every cog sits in (or within 1% of) its box
+        const float4 pb = T.box[parent];
+        const float ex = 0.01f * (pb.z - pb.x), ey = 0.01f * (pb.w - pb.y);
+        if (!(cx >= pb.x - ex && cx <= pb.z + ex && cy >= pb.y - ey && cy <= pb.w + ey)) meta->cog_outside = 1u;
+      }
       cur = parent;
       cur_count = total;
       parent = lp.w;

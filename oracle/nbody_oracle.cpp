@@ -1082,6 +1082,58 @@ int orc_world_update(void *h, int kind, float delta, float theta, float x0, floa
   return 0;
 }
 
+
+// ---- design tool: statistics of a group-cooperative walk (G tree-order-adjacent bodies walk the
+// union of their private walks, every body keeping its own decisions).  Not used by any test of
+// the product; it sizes the GPU traversal (SIMD efficiency of warp-cooperative walks).
+// out[0]=groups, [1]=internal node visits, [2]=leaf visits, [3]=sum of unmasked bodies at internal
+// visits (= opening tests), [4]=accepted (node interactions), [5]=leaf-body pair interactions,
+// [6]=sum over leaf visits of leaf body count (uniform loop trips), [7]=sum of unmasked bodies at leaf visits
+int orc_group_walk_stats(void *h, float theta, int G, double *out) {
+  OrcTree *T = (OrcTree *)h;
+  const FlatTree &t = T->flat;
+  const uint32_t nn = (uint32_t)t.depth.size();
+  const size_t n = t.n;
+  double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma omp parallel
+  {
+    double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<uint32_t> resume(G);
+#pragma omp for schedule(dynamic, 64)
+    for (long long g0 = 0; g0 < (long long)n; g0 += G) {
+      int gs = (int)std::min<size_t>(G, n - g0);
+      for (int k = 0; k < gs; ++k) resume[k] = 0;
+      a[0] += 1;
+      uint32_t cur = 0;
+      while (cur < nn) {
+        if (t.leaf[cur]) {
+          int act = 0;
+          for (int k = 0; k < gs; ++k) act += (cur >= resume[k]);
+          a[2] += 1; a[6] += t.count[cur]; a[7] += act; a[5] += (double)act * t.count[cur];
+          cur = cur + 1;
+        } else {
+          a[1] += 1;
+          bool any_open = false;
+          V2 cog{t.cogx[cur], t.cogy[cur]};
+          for (int k = 0; k < gs; ++k) {
+            if (cur < resume[k]) continue;
+            a[3] += 1;
+            V2 p{t.sx[g0 + k], t.sy[g0 + k]};
+            bool contains = p.y > t.y0[cur] && p.x > t.x0[cur] && p.x < t.x1[cur] && p.y < t.y1[cur];
+            if (!contains && t.s2[cur] < dist2(p, cog) * theta * theta) { a[4] += 1; resume[k] = t.skip[cur]; }
+            else any_open = true;
+          }
+          cur = any_open ? cur + 1 : t.skip[cur];
+        }
+      }
+    }
+#pragma omp critical
+    for (int k = 0; k < 8; ++k) acc[k] += a[k];
+  }
+  for (int k = 0; k < 8; ++k) out[k] = acc[k];
+  return 0;
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -80,7 +80,9 @@ def test_accel_fast_within_tolerance(tree, okind):
     ax, ay = w.accel(c)
     T = ob.Tree(okind, p["x"], p["y"], p["weight"])
     rx, ry, ni, nt, _ = T.accel(theta)
-    assert c.interactions == ni and c.node_tests == nt  # same opening decisions
+    # FAST evaluates the opening test as s2 < fma(dy,dy,dx*dx)*theta^2: decisions may flip only when
+    # the two sides agree to ~1e-7, so the interaction lists agree to a few parts per million
+    assert abs(int(c.interactions) - ni) <= 1e-5 * ni and abs(int(c.node_tests) - nt) <= 1e-5 * nt
     err = ob.normwise_err(ax, ay, rx, ry)
     assert err <= 1e-5, err
     w.close()
