@@ -750,7 +750,7 @@ int nb_get_tree(nb_ctx *c, const nb_tree_view *v) {
   for (uint32_t i = 0; i < nn; ++i) {
     if (v->node_skip) v->node_skip[i] = link[i].x;
     if (v->node_start) v->node_start[i] = link[i].y;
-    if (v->node_count) v->node_count[i] = link[i].z & ~kLeafBit;
+    if (v->node_count) v->node_count[i] = link[i].z & kCountMask;
     if (v->node_leaf) v->node_leaf[i] = (link[i].z & kLeafBit) ? 1 : 0;
     if (v->node_parent) v->node_parent[i] = link[i].w;
     if (v->node_cogx) v->node_cogx[i] = cm[i].x;

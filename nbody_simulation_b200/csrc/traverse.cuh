@@ -45,6 +45,13 @@ __device__ __forceinline__ void force_from_diff(float dx, float dy, float d2, fl
   }
 }
 
+// One 256-bit load of the interleaved node record (cm, link): sm_100 has ld.global.v8.
+__device__ __forceinline__ void load_node(const float4 *p, float4 &c, uint4 &l) {
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w), "=r"(l.x), "=r"(l.y), "=r"(l.z), "=r"(l.w)
+      : "l"(p));
+}
+
 template <bool EXACT, bool COUNT>
 __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict__ box,
                                                        const float4 *__restrict__ node /* [2i]=cm, [2i+1]=link */,
@@ -70,12 +77,12 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
   const bool need_contains = EXACT || !(theta2 <= 0.45f) || meta->cog_outside != 0;
   uint32_t cur = 0;
   while (cur < n_nodes) {
-    const float4 *np = node + 2 * (size_t)cur;
-    const float4 lf = np[1];
-    const uint4 l = make_uint4(__float_as_uint(lf.x), __float_as_uint(lf.y), __float_as_uint(lf.z), 0u);
+    float4 c;
+    uint4 l;
+    load_node(node + 2 * (size_t)cur, c, l);
     const bool active = cur >= resume;
     if (l.z & kLeafBit) {
-      const uint32_t k = l.z & ~kLeafBit;
+      const uint32_t k = l.z & kCountMask;
       const float4 *bp = sbody + l.y;
       if (active) {
 #pragma unroll 4
@@ -87,7 +94,6 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
       if (COUNT && active) n_inter += k;
       cur = cur + 1;
     } else {
-      const float4 c = np[0];
       float dx, dy, d2;
       bool far;
       if (EXACT) {

@@ -41,6 +41,8 @@ struct TreeArrays {
 };
 
 constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kTwigBit = 0x40000000u; // internal node whose children are all leaves
+constexpr uint32_t kCountMask = 0x3fffffffu;
 
 __global__ void tree_prepare_kernel(const unsigned long long *__restrict__ skeys, uint32_t n, int quad_mode,
                                     Meta *meta) {
@@ -232,11 +234,15 @@ __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__
     T.arrive[p] = 0;
     const uint4 l = T.link(p);
     if (l.z & kLeafBit) continue;
+    bool all_leaf = true;
     for (uint32_t c = p + 1; c < l.x;) {
       uint32_t *lc = reinterpret_cast<uint32_t *>(&T.link(c));
       lc[3] = p;
+      all_leaf = all_leaf && (lc[2] & kLeafBit);
       c = lc[0];
     }
+    // a "twig": opening it means summing every body below it, in tree order (main.rs:351-363)
+    if (all_leaf) reinterpret_cast<uint32_t *>(&T.link(p))[2] = l.z | kTwigBit;
   }
 }
 
@@ -257,7 +263,7 @@ __global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__res
   for (uint32_t p = tid; p < n_nodes; p += nth) {
     const uint4 l = T.link(p);
     if (!(l.z & kLeafBit)) continue;
-    const uint32_t s = l.y, k = l.z & ~kLeafBit;
+    const uint32_t s = l.y, k = l.z & kCountMask;
     if (k <= 64) {
       uint32_t slot[64], bid[64];
       for (uint32_t j = 0; j < k; ++j) {
@@ -323,7 +329,7 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ me
   for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < n_nodes; node += gridDim.x * blockDim.x) {
     uint4 l = T.link(node);
     if (!(l.z & kLeafBit)) continue;
-    const uint32_t s = l.y, k = l.z & ~kLeafBit;
+    const uint32_t s = l.y, k = l.z & kCountMask;
     float ax = 0.f, ay = 0.f;
     uint32_t mass = 0;
     float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
@@ -359,7 +365,7 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ me
       __threadfence();
       const uint32_t old = atomicAdd(&T.arrive[parent], cur_count);
       const uint4 lp = T.link(parent);
-      const uint32_t total = lp.z & ~kLeafBit;
+      const uint32_t total = lp.z & kCountMask;
       if (old + cur_count != total) break;
       __threadfence();
       uint32_t pm = 0;
