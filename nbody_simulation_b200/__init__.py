@@ -64,6 +64,13 @@ def generate_scene(scene, seed=1, n=0):
     return out
 
 
+def shard_range(n, rank, n_ranks):
+    """Morton-range sharding rule of the multi-GPU step (host arithmetic inside the library)."""
+    f, c = C.c_uint64(), C.c_uint64()
+    _lib.lib().nb_shard_range(int(n), int(rank), int(n_ranks), C.byref(f), C.byref(c))
+    return f.value, c.value
+
+
 def pinned_particles(n):
     """A particle array in pinned host memory (nb_host_alloc); keep the returned owner alive."""
     L = _lib.lib()

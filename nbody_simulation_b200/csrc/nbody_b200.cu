@@ -146,14 +146,10 @@ void free_bodies(BodyArrays &b) {
 
 // owned range of tree positions for this rank
 void owned_range(const nb_ctx *c, uint32_t &first, uint32_t &count) {
-  if (c->n_ranks <= 1) {
-    first = 0;
-    count = c->n;
-    return;
-  }
-  uint32_t per = cdiv(c->n, (uint32_t)c->n_ranks);
-  first = std::min(c->n, per * (uint32_t)c->rank);
-  count = std::min(per, c->n - first);
+  uint64_t f, n;
+  nb_shard_range(c->n, c->rank, c->n_ranks, &f, &n);
+  first = (uint32_t)f;
+  count = (uint32_t)n;
 }
 
 // ---- one build: morton -> sort -> topology -> up-sweep (BVHTree::from + calculate_gravity,
@@ -819,6 +815,18 @@ int nb_comm_init(nb_ctx *c, int rank, int n_ranks, const uint8_t id[NB_UNIQUE_ID
   c->rank = rank;
   c->n_ranks = n_ranks;
   return NB_OK;
+}
+
+void nb_shard_range(uint64_t n, int rank, int n_ranks, uint64_t *first, uint64_t *count) {
+  if (n_ranks <= 1) {
+    *first = 0;
+    *count = n;
+    return;
+  }
+  const uint64_t per = (n + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+  const uint64_t f = std::min<uint64_t>(n, per * (uint64_t)rank);
+  *first = f;
+  *count = std::min<uint64_t>(per, n - f);
 }
 
 int nb_comm_owned_range(nb_ctx *c, uint64_t *first, uint64_t *count) {

@@ -1,0 +1,65 @@
+"""Multi-GPU parity check (run under torchrun on a box with >= 2 GPUs; not collected by pytest):
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+      --master-port 29511 tests/multi_gpu_check.py
+
+Every rank steps the same scene with Morton-range sharding + NCCL all-gather and must end with
+state bit-identical to a single-GPU run (and therefore to the oracle, see test_gpu_parity.py)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import nbody_simulation_b200 as nb  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ok = True
+    for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH):
+        for n in (100_003, 7):
+            p = nb.generate_scene(nb.NB_SCENE_TWO_GALAXY, 3, n)
+            steps = 5
+            w = nb.World(len(p), theta=0.6, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_EXACT, device=local)
+            uid = torch.zeros(nb._lib.NB_UNIQUE_ID_BYTES, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                uid.copy_(torch.from_numpy(nb.World.comm_unique_id()))
+            dist.broadcast(uid, 0)
+            w.comm_init(rank, world, uid.cpu().numpy())
+            w.set_particles(p)
+            c = nb.Counting()
+            w.step(steps, c)
+            q = w.particles
+            ref = nb.World(len(p), theta=0.6, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_EXACT, device=local)
+            ref.set_particles(p)
+            rc = nb.Counting()
+            ref.step(steps, rc)
+            r = ref.particles
+            same = all(np.array_equal(q[k].view(np.uint32), r[k].view(np.uint32)) for k in ("x", "y", "vx", "vy", "weight"))
+            tot = torch.tensor([float(c.interactions)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tot)
+            counts_ok = int(tot.item()) == rc.interactions
+            f, cnt = w.owned_range()
+            print(f"rank {rank}/{world} tree={tree} n={len(p)} owned=[{f},{f + cnt}) bit-identical={same} "
+                  f"interactions sum={int(tot.item())} single={rc.interactions} ok={counts_ok} "
+                  f"exchange_ms/step={c.exchange / steps * 1e3:.3f}", flush=True)
+            ok = ok and same and counts_ok
+            w.close()
+            ref.close()
+    flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    if flag.item() != 1.0:
+        raise SystemExit("MULTI-GPU PARITY FAILED")
+    if rank == 0:
+        print("multi-gpu parity ok")
+
+
+if __name__ == "__main__":
+    main()
