@@ -26,6 +26,10 @@
 
 using namespace nb;
 
+static_assert(sizeof(nb_particle) == 24, "nb_particle mirrors the 24-byte Particle (src/main.rs:193-198)");
+static_assert(sizeof(nb_config) == 88 && sizeof(nb_counting) == 96 && sizeof(nb_tree_info) == 72,
+              "C ABI struct layout (tests/test_abi.py and the ctypes binding rely on it)");
+
 namespace {
 
 thread_local std::string g_create_error;
