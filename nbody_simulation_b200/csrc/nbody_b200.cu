@@ -382,7 +382,7 @@ void nb_destroy(nb_ctx *c) {
   free_bodies(c->body[0]);
   free_bodies(c->body[1]);
   for (int i = 0; i < 2; ++i) { cudaFree(c->keys[i]); cudaFree(c->vals[i]); }
-  cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.table); cudaFree(c->sort.bsum);
+  cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.ghist); cudaFree(c->sort.tickets); cudaFree(c->sort.status); cudaFree(c->sort.bsum);
   cudaFree(c->T.box); cudaFree(c->T.node); cudaFree(c->T.mass); cudaFree(c->T.depth);
   cudaFree(c->T.bmax); cudaFree(c->T.arrive);
   cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
@@ -394,8 +394,8 @@ void nb_destroy(nb_ctx *c) {
 }
 
 nb_ctx *nb_create(const nb_config *cfg) {
-  if (!cfg || cfg->n_max == 0 || cfg->n_max > 0x7fff0000ull) {
-    fail(nullptr, NB_ERR_INVALID, "nb_create: n_max must be in [1, 2^31)");
+  if (!cfg || cfg->n_max == 0 || cfg->n_max > 0x3fff0000ull) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: n_max must be in [1, 2^30)");
     return nullptr;
   }
   if (cfg->tree_kind != NB_TREE_QUAD && cfg->tree_kind != NB_TREE_LBVH) {
@@ -442,9 +442,11 @@ nb_ctx *nb_create(const nb_config *cfg) {
   }
   NB_TRY(dmalloc(&c->leafdepth, na));
   NB_TRY(dmalloc(&c->nstart, na));
-  const size_t table = sort_table_entries((uint32_t)na);
-  NB_TRY(dmalloc(&c->sort.table, table));
-  NB_TRY(dmalloc(&c->sort.bsum, std::max<size_t>(table / kScanTile + 16, na / kScanTile + 16)));
+  c->sort.status_words = sort_status_words((uint32_t)na);
+  NB_TRY(dmalloc(&c->sort.ghist, (size_t)4096));
+  NB_TRY(dmalloc(&c->sort.tickets, (size_t)16));
+  NB_TRY(dmalloc(&c->sort.status, c->sort.status_words));
+  NB_TRY(dmalloc(&c->sort.bsum, na / kScanTile + 16));
   const size_t ncap = 2 * na + 65536;
   c->T.capacity = (uint32_t)std::min<size_t>(ncap, 0xfffffff0u);
   NB_TRY(dmalloc(&c->T.box, (size_t)c->T.capacity));

@@ -1,9 +1,13 @@
-// radix_sort.cuh — K2: stable LSD radix sort of (u64 Morton key, u32 body slot) pairs.
+// radix_sort.cuh — K2: stable LSD radix sort of (u64 Morton key, u32 body slot) pairs, onesweep style.
 //
-// Round-1 formulation: per pass  tile histogram -> device-wide scan of the [digit][tile] table ->
-// stable scatter.  Ranking inside a tile is warp-synchronous (match_any multi-split) with
-// per-warp digit counters in shared memory, so the pass is stable without any sorting network.
-// HBM traffic per pass: keys read twice (8+8 B), values once (4 B), pairs written once (12 B).
+//   1 launch : histograms of ALL passes from one read of the keys (8 B/key)
+//   1 launch : exclusive scan of each pass's histogram (tiny)
+//   per pass : ONE kernel — each tile ranks its keys (warp match_any multi-split, per-warp digit
+//              counters in shared memory => stable), gets its global digit offsets by decoupled
+//              look-back over the preceding tiles, stages the tile in shared memory in output order
+//              and writes coalesced runs.
+// HBM traffic: 8 B + passes x (12 B read + 12 B written) per pair  (6 passes: 152 B/pair).
+// Tiles take their index from an atomic ticket, so a tile only ever waits on tiles that already run.
 #pragma once
 #include "common.cuh"
 #include "scan.cuh"
@@ -12,124 +16,231 @@ namespace nb {
 
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
-constexpr int kSortRounds = 16;                                // 32-element rounds per warp
-constexpr int kSortTile = kSortThreads * kSortRounds;          // 4096 elements per tile
+constexpr int kSortRounds = 16;                       // 32-element rounds per warp
+constexpr int kSortTile = kSortThreads * kSortRounds; // 4096 pairs per tile
+constexpr int kSortMaxPasses = 7;
+constexpr int kSortMaxRadix = 512;
 
-template <int RADIX_BITS>
-__global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(const unsigned long long *__restrict__ keys, uint32_t n,
-                                                                 int shift, uint32_t nblocks,
-                                                                 uint32_t *__restrict__ table) {
-  constexpr int RADIX = 1 << RADIX_BITS;
-  __shared__ uint32_t hist[RADIX];
-  for (int d = threadIdx.x; d < RADIX; d += kSortThreads) hist[d] = 0;
+constexpr uint32_t kFlagLocal = 1u << 30;     // status word: tile-local digit count
+constexpr uint32_t kFlagInclusive = 2u << 30; // status word: inclusive prefix over tiles 0..t
+constexpr uint32_t kStatusValue = (1u << 30) - 1u;
+
+struct SortPlan { // digit layout of one sort, passed by value to the kernels
+  int passes;
+  int shift[kSortMaxPasses];
+  int bits[kSortMaxPasses];
+  int hist_off[kSortMaxPasses]; // offset of the pass's bins in the histogram arrays
+  int hist_total;
+};
+
+inline SortPlan make_sort_plan(int key_bits) { // 8-bit digits; a 9-bit last digit absorbs an odd top bit
+  SortPlan p{};
+  int shift = 0, off = 0;
+  while (shift < key_bits) {
+    int b = (key_bits - shift == 9) ? 9 : 8;
+    if (key_bits - shift < 8) b = key_bits - shift;
+    p.shift[p.passes] = shift;
+    p.bits[p.passes] = b;
+    p.hist_off[p.passes] = off;
+    off += 1 << b;
+    shift += b;
+    ++p.passes;
+  }
+  p.hist_total = off;
+  return p;
+}
+
+// All passes' histograms in one read of the keys.
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long *__restrict__ keys, uint32_t n,
+                                                             SortPlan plan, uint32_t *__restrict__ ghist) {
+  extern __shared__ uint32_t sh[];
+  for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x) sh[i] = 0;
   __syncthreads();
-  const uint32_t base = blockIdx.x * kSortTile;
-#pragma unroll 4
-  for (int k = 0; k < kSortRounds; ++k) {
-    uint32_t i = base + k * kSortThreads + threadIdx.x;
-    if (i < n) atomicAdd(&hist[(uint32_t)(keys[i] >> shift) & (RADIX - 1)], 1u);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned long long k = keys[i];
+    for (int p = 0; p < plan.passes; ++p)
+      atomicAdd(&sh[plan.hist_off[p] + ((uint32_t)(k >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
   }
   __syncthreads();
-  for (int d = threadIdx.x; d < RADIX; d += kSortThreads) table[(size_t)d * nblocks + blockIdx.x] = hist[d];
+  for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x)
+    if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// Exclusive scan per pass (one block per pass); also resets the tile tickets.
+__global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restrict__ ghist, SortPlan plan,
+                                                             uint32_t *__restrict__ tickets) {
+  const int p = blockIdx.x;
+  const int radix = 1 << plan.bits[p];
+  uint32_t *h = ghist + plan.hist_off[p];
+  const uint32_t v = ((int)threadIdx.x < radix) ? h[threadIdx.x] : 0u;
+  uint32_t tot;
+  const uint32_t ex = block_exclusive_scan<512>(v, tot);
+  if ((int)threadIdx.x < radix) h[threadIdx.x] = ex;
+  if (threadIdx.x == 0) tickets[p] = 0;
 }
 
 template <int RADIX_BITS>
-__global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(
+__global__ void __launch_bounds__(kSortThreads) sort_onesweep_kernel(
     const unsigned long long *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
     unsigned long long *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int shift,
-    uint32_t nblocks, const uint32_t *__restrict__ table_scanned) {
+    const uint32_t *__restrict__ gbase /* scanned histogram of this pass */, uint32_t *ticket,
+    volatile uint32_t *status /* [tiles][RADIX], zeroed */) {
   constexpr int RADIX = 1 << RADIX_BITS;
-  __shared__ uint32_t cnt[kSortWarps][RADIX];
-  __shared__ uint32_t gofs[RADIX];
+  constexpr int DPT = RADIX / kSortThreads; // digits per thread in the look-back (1 or 2)
+  __shared__ uint16_t cnt[kSortWarps][RADIX]; // per-warp digit counts (<= 512) -> exclusive over warps (< 4096)
+  __shared__ uint32_t tile_ofs[RADIX];        // exclusive digit offsets inside the tile
+  __shared__ uint32_t goff[RADIX];            // global position of the tile's first element of each digit
+  __shared__ unsigned long long stage[kSortTile];
+  __shared__ uint32_t tile_s;
   const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const unsigned lt = (1u << lane) - 1u;
+  if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1u);
   for (int d = threadIdx.x; d < RADIX * kSortWarps; d += kSortThreads) (&cnt[0][0])[d] = 0;
-  for (int d = threadIdx.x; d < RADIX; d += kSortThreads) gofs[d] = table_scanned[(size_t)d * nblocks + blockIdx.x];
   __syncthreads();
+  const uint32_t tile = tile_s;
+  const uint32_t tbase = tile * kSortTile;
+  const uint32_t tcount = (n - tbase < (uint32_t)kSortTile) ? n - tbase : (uint32_t)kSortTile;
 
-  // warp w owns the contiguous chunk [base + w*512, base + (w+1)*512) in 16 rounds of 32
-  const uint32_t wbase = blockIdx.x * kSortTile + w * (32 * kSortRounds);
+  // warp w owns the contiguous chunk [tbase + w*512, +512) in 16 rounds of 32 (load order == rank order)
+  const uint32_t wbase = tbase + w * (32 * kSortRounds);
   unsigned long long key[kSortRounds];
-  uint32_t val[kSortRounds];
-  uint32_t rank[kSortRounds]; // digit in the high half, rank in the low half (both < 65536)
+  uint32_t rank[kSortRounds]; // digit << 16 | rank among equal digits in this warp's chunk
 #pragma unroll
   for (int k = 0; k < kSortRounds; ++k) {
-    uint32_t i = wbase + k * 32 + lane;
-    bool valid = i < n;
-    key[k] = valid ? keys_in[i] : 0ull;
-    val[k] = valid ? vals_in[i] : 0u;
+    const uint32_t i = wbase + k * 32 + lane;
+    key[k] = (i < n) ? keys_in[i] : 0ull;
   }
 #pragma unroll
   for (int k = 0; k < kSortRounds; ++k) {
-    uint32_t i = wbase + k * 32 + lane;
-    bool valid = i < n;
-    uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
-    uint32_t m = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
-    uint32_t prev = valid ? cnt[w][d] : 0u;
+    const uint32_t i = wbase + k * 32 + lane;
+    const bool valid = i < n;
+    const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
+    const uint32_t m = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
+    const uint32_t prev = valid ? cnt[w][d] : 0u;
     __syncwarp();
-    uint32_t r = __popc(m & lt);
-    if (valid && r == 0) cnt[w][d] = prev + __popc(m);
+    const uint32_t r = __popc(m & lt);
+    if (valid && r == 0) cnt[w][d] = (uint16_t)(prev + __popc(m));
     __syncwarp();
     rank[k] = (d << 16) | (prev + r);
   }
   __syncthreads();
-  // exclusive scan over the warps, per digit
-  for (int d = threadIdx.x; d < RADIX; d += kSortThreads) {
+  // per digit: exclusive scan over the warps, tile total, publish, look back
+  uint32_t dtot[DPT];
+#pragma unroll
+  for (int q = 0; q < DPT; ++q) {
+    const int d = threadIdx.x + q * kSortThreads;
     uint32_t run = 0;
 #pragma unroll
     for (int ww = 0; ww < kSortWarps; ++ww) {
-      uint32_t t = cnt[ww][d];
-      cnt[ww][d] = run;
+      const uint32_t t = cnt[ww][d];
+      cnt[ww][d] = (uint16_t)run;
       run += t;
+    }
+    dtot[q] = run;
+    status[(size_t)tile * RADIX + d] = (tile == 0 ? kFlagInclusive : kFlagLocal) | run;
+  }
+  // exclusive scan of the tile totals over the digits -> tile_ofs (thread t owns digits t, t+256)
+  {
+    uint32_t tot0;
+    const uint32_t e0 = block_exclusive_scan<kSortThreads>(dtot[0], tot0);
+    tile_ofs[threadIdx.x] = e0;
+    if (DPT == 2) {
+      uint32_t tot1;
+      const uint32_t e1 = block_exclusive_scan<kSortThreads>(dtot[DPT - 1], tot1);
+      tile_ofs[threadIdx.x + (DPT - 1) * kSortThreads] = tot0 + e1;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < DPT; ++q) {
+    const int d = threadIdx.x + q * kSortThreads;
+    uint32_t prefix = 0;
+    if (tile > 0) {
+      int t = (int)tile - 1;
+      for (;;) {
+        uint32_t sv;
+        do { sv = status[(size_t)t * RADIX + d]; } while ((sv >> 30) == 0u);
+        prefix += sv & kStatusValue;
+        if ((sv >> 30) == 2u) break;
+        --t;
+      }
+      status[(size_t)tile * RADIX + d] = kFlagInclusive | (prefix + dtot[q]);
+    }
+    goff[d] = gbase[d] + prefix;
+  }
+  __syncthreads();
+  // stage the keys in output order, then write coalesced runs
+  uint32_t pos[kSortRounds];
+#pragma unroll
+  for (int k = 0; k < kSortRounds; ++k) {
+    const uint32_t d = rank[k] >> 16;
+    pos[k] = tile_ofs[d] + cnt[w][d] + (rank[k] & 0xffffu);
+    if (wbase + k * 32 + lane < n) stage[pos[k]] = key[k];
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < tcount; i += kSortThreads) {
+    const unsigned long long kk = stage[i];
+    const uint32_t d = (uint32_t)(kk >> shift) & (RADIX - 1);
+    keys_out[goff[d] + (i - tile_ofs[d])] = kk;
+  }
+  __syncthreads();
+  uint32_t *vstage = reinterpret_cast<uint32_t *>(stage);
+  uint32_t *dstage = vstage + kSortTile; // digit of each staged slot (second half of the buffer)
+#pragma unroll
+  for (int k = 0; k < kSortRounds; ++k) {
+    const uint32_t i = wbase + k * 32 + lane;
+    if (i < n) {
+      vstage[pos[k]] = vals_in[i];
+      dstage[pos[k]] = rank[k] >> 16;
     }
   }
   __syncthreads();
-#pragma unroll
-  for (int k = 0; k < kSortRounds; ++k) {
-    uint32_t i = wbase + k * 32 + lane;
-    if (i < n) {
-      uint32_t d = rank[k] >> 16;
-      uint32_t pos = gofs[d] + cnt[w][d] + (rank[k] & 0xffffu);
-      keys_out[pos] = key[k];
-      vals_out[pos] = val[k];
-    }
+  for (uint32_t i = threadIdx.x; i < tcount; i += kSortThreads) {
+    const uint32_t d = dstage[i];
+    vals_out[goff[d] + (i - tile_ofs[d])] = vstage[i];
   }
 }
 
 struct SortScratch {
-  uint32_t *table;  // [512 * nblocks_max]
-  uint32_t *bsum;   // scan block sums
+  uint32_t *ghist;    // [hist_total] all passes' histograms, scanned in place
+  uint32_t *tickets;  // [passes]
+  uint32_t *status;   // [passes][tiles][radix]
+  size_t status_words;
+  uint32_t *bsum;     // scratch for the device-wide scan used by the tree build
 };
 
-inline size_t sort_table_entries(uint32_t n_max) {
-  uint32_t nb = (n_max + kSortTile - 1) / kSortTile;
-  if (nb == 0) nb = 1;
-  return (size_t)512 * nb;
+inline size_t sort_status_words(uint32_t n_max) {
+  size_t tiles = ((size_t)n_max + kSortTile - 1) / kSortTile;
+  if (tiles == 0) tiles = 1;
+  return tiles * (size_t)(5 * 256 + 512 + 256); // up to 7 passes, one of them 9 bits wide
 }
 
-// Sorts `bits` low key bits (48 or 49) in 6 passes: five 8-bit digits, then the remaining 8 or 9.
-// Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
+// Sorts the low `bits` key bits.  Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
 inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
                             uint32_t *vals_b, uint32_t n, int bits, const SortScratch &sc, cudaStream_t st) {
   if (n == 0) return 0;
-  const uint32_t nblocks = (n + kSortTile - 1) / kSortTile;
+  const SortPlan plan = make_sort_plan(bits);
+  const uint32_t tiles = (n + kSortTile - 1) / kSortTile;
+  size_t need = 0;
+  for (int p = 0; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
+  cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);
+  cudaMemsetAsync(sc.status, 0, need * sizeof(uint32_t), st);
+  const uint32_t hblocks = tiles < (uint32_t)kSMs * 4u ? tiles : (uint32_t)kSMs * 4u;
+  g_launches += 2 + plan.passes;
+  sort_histogram_kernel<<<hblocks, 256, plan.hist_total * sizeof(uint32_t), st>>>(keys_a, n, plan, sc.ghist);
+  sort_scan_hist_kernel<<<plan.passes, 512, 0, st>>>(sc.ghist, plan, sc.tickets);
   unsigned long long *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
   int which = 0;
-  int shift = 0;
-  while (shift < bits) {
-    int rb = (bits - shift == 9) ? 9 : 8;
-    g_launches += 2;
-    if (rb == 8) {
-      sort_hist_kernel<8><<<nblocks, kSortThreads, 0, st>>>(kin, n, shift, nblocks, sc.table);
-      exclusive_scan_u32(sc.table, sc.table, nullptr, 256u * nblocks, sc.bsum, nullptr, st);
-      sort_scatter_kernel<8><<<nblocks, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, shift, nblocks, sc.table);
-    } else {
-      sort_hist_kernel<9><<<nblocks, kSortThreads, 0, st>>>(kin, n, shift, nblocks, sc.table);
-      exclusive_scan_u32(sc.table, sc.table, nullptr, 512u * nblocks, sc.bsum, nullptr, st);
-      sort_scatter_kernel<9><<<nblocks, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, shift, nblocks, sc.table);
-    }
-    shift += rb;
+  size_t soff = 0;
+  for (int p = 0; p < plan.passes; ++p) {
+    const uint32_t *gb = sc.ghist + plan.hist_off[p];
+    if (plan.bits[p] == 9)
+      sort_onesweep_kernel<9><<<tiles, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, plan.shift[p], gb,
+                                                             sc.tickets + p, sc.status + soff);
+    else
+      sort_onesweep_kernel<8><<<tiles, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, plan.shift[p], gb,
+                                                             sc.tickets + p, sc.status + soff);
+    soff += (size_t)tiles << plan.bits[p];
     unsigned long long *tk = kin; kin = kout; kout = tk;
     uint32_t *tv = vin; vin = vout; vout = tv;
     which ^= 1;
