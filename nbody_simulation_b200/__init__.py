@@ -202,6 +202,11 @@ class World:
         self._ck(self._L.nb_accel_direct(self._ctx, first, count, ax.ctypes.data, ay.ctypes.data, C.byref(sec)))
         return ax, ay, sec.value
 
+    def measure_fp32(self, kind):
+        r = C.c_double(0.0)
+        self._ck(self._L.nb_measure_fp32(self._ctx, int(kind), C.byref(r)))
+        return r.value
+
     def flush_l2(self):
         self._ck(self._L.nb_flush_l2(self._ctx))
 

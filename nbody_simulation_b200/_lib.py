@@ -135,6 +135,7 @@ def load(path=LIB_PATH):
         "nb_host_alloc": (vp, [C.c_size_t]),
         "nb_host_free": (None, [vp]),
         "nb_flush_l2": (C.c_int, [vp]),
+        "nb_measure_fp32": (C.c_int, [vp, C.c_int, P(C.c_double)]),
         "nb_get_tree_info": (C.c_int, [vp, P(NbTreeInfo)]),
         "nb_get_tree": (C.c_int, [vp, P(NbTreeView)]),
         "nb_draw": (C.c_int, [vp, vp, C.c_uint32]),

@@ -22,6 +22,7 @@
 #include "radix_sort.cuh"
 #include "scan.cuh"
 #include "traverse.cuh"
+#include "ubench.cuh"
 #include "tree_build.cuh"
 
 using namespace nb;
@@ -491,6 +492,38 @@ void *nb_host_alloc(size_t bytes) {
 }
 void nb_host_free(void *p) {
   if (p) cudaFreeHost(p);
+}
+
+// FP32 pipe microbenchmark (see ubench.cuh).  *rate = lane-operations per second of the kind's unit:
+// kinds 0/1 flop/s, kinds 2/3 pair interactions/s.
+int nb_measure_fp32(nb_ctx *c, int kind, double *rate) {
+  if (!c || !rate || kind < 0 || kind > 3) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  const int blocks = kSMs * 8, threads = 256, iters = 20000;
+  float *out = reinterpret_cast<float *>(c->sacc);
+  cudaEvent_t e0 = next_event(c), e1 = next_event(c);
+  if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+  double best = 0.0;
+  for (int rep = 0; rep < 4; ++rep) {
+    NB_CUDA(c, cudaEventRecord(e0, c->stream));
+    switch (kind) {
+    case 0: fp32_ubench_kernel<0><<<blocks, threads, 0, c->stream>>>(out, iters, 0.5f); break;
+    case 1: fp32_ubench_kernel<1><<<blocks, threads, 0, c->stream>>>(out, iters, 0.5f); break;
+    case 2: fp32_ubench_kernel<2><<<blocks, threads, 0, c->stream>>>(out, iters, 0.5f); break;
+    default: fp32_ubench_kernel<3><<<blocks, threads, 0, c->stream>>>(out, iters, 0.5f); break;
+    }
+    NB_CUDA(c, cudaEventRecord(e1, c->stream));
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    NB_CUDA(c, cudaEventElapsedTime(&ms, e0, e1));
+    const double lanes = (double)blocks * threads * iters;
+    const double per = kind == 0 ? 16.0 * 2.0 : kind == 1 ? 8.0 * 4.0 : 8.0; // flop or interactions per lane-iter
+    const double r = lanes * per / (ms * 1e-3);
+    if (rep > 0 && r > best) best = r;
+  }
+  c->ev_used = 0;
+  *rate = best;
+  return NB_OK;
 }
 
 int nb_flush_l2(nb_ctx *c) {
