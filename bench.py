@@ -67,7 +67,7 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
@@ -242,7 +242,6 @@ def main():
         w.step(1, c)
     barrier()
     wall = time.perf_counter() - t0
-    clocks = sampler.stop() if sampler else None
     dev_s = allreduce(c.total, dist.ReduceOp.MAX if dist else None)
     inter = allreduce(replay_inter, dist.ReduceOp.SUM if dist else None)
     rank_inter = replay_inter
@@ -273,10 +272,13 @@ def main():
                "steps_per_s": args.steps / e2e_s, "call": "nb_world_update (pinned host nb_particle[])"}
         del host, owner
 
+    clocks = sampler.stop() if sampler else None
     if rank == 0:
         peaks, peak_src = measured_peaks()
         fmax = float(peaks.get("sm_max_mhz", 1965.0))
-        fp32_peak = 148 * 128 * 2 * fmax * 1e6 / 1e12  # TFLOP/s
+        fp32_nominal = 148 * 128 * 2 * fmax * 1e6 / 1e12  # TFLOP/s
+        fp32_peak = w.measure_fp32(0) / 1e12              # measured now: scalar FFMA chains (burst)
+        pair_ceiling = w.measure_fp32(2)                  # pair force on register operands, interactions/s
         trav_s = c.sum_gravity / args.steps
         trav_tflops = FLOP_PER_INTERACTION * (rank_inter / args.steps) / trav_s / 1e12
         traffic = None
@@ -304,9 +306,12 @@ def main():
             "gpu_launches": int(c.launches),
             "roofline": {"bound": "fp32", "kernel": "traverse_kernel", "achieved": trav_tflops,
                          "peak": fp32_peak, "unit": "TFLOP/s", "frac": trav_tflops / fp32_peak, "traffic": traffic,
-                         "peak_source": (f"148 SM x 128 lanes x 2 flop x {fmax:.0f} MHz (clocks.max.sm, {peak_src}); "
+                         "peak_source": ("FFMA microbenchmark (nb_measure_fp32 kind 0) measured in this run; "
+                                         f"nominal 148 SM x 128 lanes x 2 flop x {fmax:.0f} MHz = {fp32_nominal:.1f}; "
                                          "MEASURED_PEAKS.json holds no fp32 entry"),
-                         "flop_per_interaction": FLOP_PER_INTERACTION},
+                         "flop_per_interaction": FLOP_PER_INTERACTION,
+                         "pair_force_ceiling_interactions_per_s": pair_ceiling,
+                         "frac_of_pair_force_ceiling": (rank_inter / args.steps) / trav_s / pair_ceiling},
         }
         if e2e:
             line["e2e"] = e2e

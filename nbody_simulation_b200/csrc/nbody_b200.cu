@@ -196,10 +196,11 @@ int enqueue_build(nb_ctx *c) {
 // [first, first+count).
 int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   if (count == 0) return NB_OK;
-  const uint32_t blocks = cdiv(cdiv(count, 32), 8);
+  static const int tpb = getenv("NB_TRAVERSE_TPB") ? atoi(getenv("NB_TRAVERSE_TPB")) : 256;
+  const uint32_t blocks = cdiv(cdiv(count, 32), (uint32_t)tpb / 32u);
   g_launches += 1;
 #define NB_TRAVERSE(EX, CNT)                                                                                  \
-  traverse_kernel<EX, CNT><<<blocks, 256, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,          \
+  traverse_kernel<EX, CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,          \
                                                           c->cfg.theta, first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
   if (ex && c->counting) NB_TRAVERSE(true, true);

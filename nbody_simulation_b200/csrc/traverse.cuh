@@ -81,18 +81,48 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
     uint4 l;
     load_node(node + 2 * (size_t)cur, c, l);
     const bool active = cur >= resume;
-    if (l.z & kLeafBit) {
+    if (l.z & (kLeafBit | kTwigBit)) {
+      // terminal visit: a leaf (summed by every active lane, main.rs:351-363), or a "twig" — an internal
+      // node whose children are all leaves: lanes that accept it take its centre of gravity, lanes that
+      // open it sum every body below it in tree order; nobody descends, so the leaf children are skipped.
+      bool take = active;
+      if (!(l.z & kLeafBit)) {
+        float dx, dy, d2;
+        bool far;
+        if (EXACT) {
+          dx = __fsub_rn(c.x, px);
+          dy = __fsub_rn(c.y, py);
+          d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+          far = c.w < __fmul_rn(__fmul_rn(d2, theta), theta);
+        } else {
+          dx = c.x - px;
+          dy = c.y - py;
+          d2 = fmaf(dy, dy, dx * dx);
+          far = c.w < d2 * theta2;
+        }
+        if (need_contains) {
+          const float4 bx = box[cur];
+          const bool contains = py > bx.y && px > bx.x && px < bx.z && py < bx.w;
+          far = far && !contains;
+        }
+        if (active && far) force_from_diff<EXACT>(dx, dy, d2, c.z, ax, ay);
+        if (COUNT) {
+          n_test += active ? 1u : 0u;
+          n_inter += (active && far) ? 1u : 0u;
+        }
+        take = active && !far;
+      }
       const uint32_t k = l.z & kCountMask;
       const float4 *bp = sbody + l.y;
-      if (active) {
+      if (take) {
 #pragma unroll 4
         for (uint32_t j = 0; j < k; ++j) {
           const float4 b = bp[j];
           pair_force<EXACT>(px, py, b.x, b.y, b.z, ax, ay);
         }
       }
-      if (COUNT && active) n_inter += k;
-      cur = cur + 1;
+      if (COUNT && take) n_inter += k;
+      cur = l.x; // == cur + 1 for a leaf
     } else {
       float dx, dy, d2;
       bool far;
