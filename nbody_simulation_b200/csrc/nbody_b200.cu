@@ -170,7 +170,7 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += 7; // morton, prepare, count, emit, link, leaf-gather, up-sweep (+ sort and scan, counted there)
+  g_launches += 6; // morton, prepare, count, emit, link, finish (+ sort and scan, counted there)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st);
   c->sorted_in = which;
@@ -184,9 +184,8 @@ int enqueue_build(nb_ctx *c) {
   if (c->quad) tree_emit_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
   tree_link_kernel<<<kSMs * 8, 256, 0, st>>>(c->meta, c->T);
-  tree_leaf_gather_kernel<<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
-  if (c->quad) tree_upsweep_kernel<false><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, c->sbody);
-  else tree_upsweep_kernel<true><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, c->sbody);
+  if (c->quad) tree_finish_kernel<false, 8><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  else tree_finish_kernel<true, 8><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
   NB_CUDA(c, cudaGetLastError());
   c->tree_valid = true;
   return NB_OK;

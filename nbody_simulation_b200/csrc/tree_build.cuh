@@ -246,25 +246,88 @@ __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__
   }
 }
 
-// Leaf fix-up + gather.  Inside every leaf the bodies are put in ascending ORIGINAL id order —
-// the order QuadTree::insert fills the slots (quad_tree.rs:163-164,221-224: insertion order, and
-// subdivide re-inserts in slot order), which fixes the f32 summation order of the leaf centre of
-// gravity (quad_tree.rs:236-240) and of the leaf interactions (main.rs:355-362).  Then the
-// tree-order body array (x, y, mass as f32, mass bits) is gathered.
-__global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__restrict__ meta, TreeArrays T,
-                                                               uint32_t *__restrict__ order,
-                                                               const float *__restrict__ x, const float *__restrict__ y,
-                                                               const uint32_t *__restrict__ m,
-                                                               const uint32_t *__restrict__ id,
-                                                               float4 *__restrict__ sbody) {
+// K3c + K4 fused: leaf fix-up, gather and the atomic bottom-up up-sweep, one thread per leaf.
+//
+// Leaf fix-up: inside every leaf the bodies are put in ascending ORIGINAL id order — the order
+// QuadTree::insert fills the slots (quad_tree.rs:163-164,221-224: insertion order, and subdivide
+// re-inserts in slot order), which fixes the f32 summation order of the leaf centre of gravity
+// (quad_tree.rs:236-240) and of the leaf interactions (main.rs:355-362).  The tree-order body array
+// (x, y, mass as f32, mass bits) is gathered in the same pass and the leaf summary is formed from the
+// registers.  Then the thread climbs: at every parent it adds its subtree's body count to the parent's
+// arrival counter; the thread that completes the count owns the parent and folds the children IN CHILD
+// ORDER (deterministic).
+//   leaf:     mass = wrapping u32 sum (bvh_tree.rs:123); cog = UNWEIGHTED mean of positions
+//             (bvh_tree.rs:104-107, quad_tree.rs:236-240)
+//   internal: mass = sum of child masses; cog = sum(child.cog * (child.mass as f32)) / (mass as f32)
+//             (quad_tree.rs:253-266 folds from (0,0); bvh_tree.rs:148-154 is a*m0 + b*m1)
+//   LBVH bounds: tight AABB with min seeded f32::MAX and max seeded 0 (bvh_tree.rs:42,59),
+//             size = max - min, s2 = max(w,h)^2 as main.rs:371 computes it.
+template <bool LBVH> struct LeafAcc {
+  float ax = 0.f, ay = 0.f;
+  uint32_t mass = 0;
+  float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
+  __device__ __forceinline__ void add(float bx, float by, uint32_t mm) {
+    ax = __fadd_rn(ax, bx);
+    ay = __fadd_rn(ay, by);
+    mass += mm;
+    if (LBVH) {
+      mnx = mnx < bx ? mnx : bx; // minps
+      mny = mny < by ? mny : by;
+      mxx = mxx > bx ? mxx : bx; // maxps
+      mxy = mxy > by ? mxy : by;
+    }
+  }
+};
+
+template <bool LBVH, int MAXK>
+__global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ meta, TreeArrays T,
+                                                          uint32_t *__restrict__ order, const float *__restrict__ x,
+                                                          const float *__restrict__ y, const uint32_t *__restrict__ m,
+                                                          const uint32_t *__restrict__ id,
+                                                          float4 *__restrict__ sbody) {
   if (meta->error) return;
   const uint32_t n_nodes = meta->n_nodes, n_in = meta->n_in, n = meta->n;
   const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-  for (uint32_t p = tid; p < n_nodes; p += nth) {
-    const uint4 l = T.link(p);
+  // bodies outside the root square: targets only
+  for (uint32_t j = n_in + tid; j < n; j += nth) {
+    const uint32_t sl = order[j];
+    const uint32_t mm = m[sl];
+    sbody[j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
+  }
+  for (uint32_t node = tid; node < n_nodes; node += nth) {
+    const uint4 l = T.link(node);
     if (!(l.z & kLeafBit)) continue;
     const uint32_t s = l.y, k = l.z & kCountMask;
-    if (k <= 64) {
+    LeafAcc<LBVH> A;
+    auto place = [&](uint32_t j, uint32_t sl) {
+      order[s + j] = sl;
+      const uint32_t mm = m[sl];
+      const float bx = x[sl], by = y[sl];
+      sbody[s + j] = make_float4(bx, by, (float)mm, __uint_as_float(mm));
+      A.add(bx, by, mm);
+    };
+    if (k <= (uint32_t)MAXK) { // registers: bubble network, padding keys sort to the end
+      uint32_t slot[MAXK], bid[MAXK];
+#pragma unroll
+      for (int j = 0; j < MAXK; ++j) {
+        slot[j] = ((uint32_t)j < k) ? order[s + j] : 0u;
+        bid[j] = ((uint32_t)j < k) ? id[slot[j]] : 0xffffffffu;
+      }
+#pragma unroll
+      for (int a = 0; a < MAXK - 1; ++a) {
+#pragma unroll
+        for (int b = 0; b < MAXK - 1 - a; ++b) {
+          const bool sw = bid[b] > bid[b + 1];
+          const uint32_t t0 = sw ? bid[b + 1] : bid[b], t1 = sw ? bid[b] : bid[b + 1];
+          const uint32_t u0 = sw ? slot[b + 1] : slot[b], u1 = sw ? slot[b] : slot[b + 1];
+          bid[b] = t0; bid[b + 1] = t1;
+          slot[b] = u0; slot[b + 1] = u1;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < MAXK; ++j)
+        if ((uint32_t)j < k) place((uint32_t)j, slot[j]);
+    } else if (k <= 64) {
       uint32_t slot[64], bid[64];
       for (uint32_t j = 0; j < k; ++j) {
         slot[j] = order[s + j];
@@ -281,12 +344,7 @@ __global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__res
         slot[b + 1] = bs;
         bid[b + 1] = bi;
       }
-      for (uint32_t j = 0; j < k; ++j) {
-        const uint32_t sl = slot[j];
-        order[s + j] = sl;
-        const uint32_t mm = m[sl];
-        sbody[s + j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
-      }
+      for (uint32_t j = 0; j < k; ++j) place(j, slot[j]);
     } else { // over-full leaf at the depth cap: in-place insertion sort in global memory
       for (uint32_t a = 1; a < k; ++a) {
         uint32_t bs = order[s + a], bi = id[bs];
@@ -297,70 +355,24 @@ __global__ void __launch_bounds__(128) tree_leaf_gather_kernel(const Meta *__res
         }
         order[s + b + 1] = bs;
       }
-      for (uint32_t j = 0; j < k; ++j) {
-        const uint32_t sl = order[s + j];
-        const uint32_t mm = m[sl];
-        sbody[s + j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
-      }
-    }
-  }
-  // bodies outside the root square: targets only
-  for (uint32_t j = n_in + tid; j < n; j += nth) {
-    const uint32_t sl = order[j];
-    const uint32_t mm = m[sl];
-    sbody[j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
-  }
-}
-
-// K4: atomic bottom-up up-sweep.  One thread per leaf computes the leaf summary, then climbs:
-// at every parent it adds its subtree's body count to the parent's arrival counter; the thread
-// that completes the count owns the parent and folds the children IN CHILD ORDER (deterministic).
-//   leaf:     mass = wrapping u32 sum (bvh_tree.rs:123); cog = UNWEIGHTED mean of positions
-//             (bvh_tree.rs:104-107, quad_tree.rs:236-240)
-//   internal: mass = sum of child masses; cog = sum(child.cog * (child.mass as f32)) / (mass as f32)
-//             (quad_tree.rs:253-266 folds from (0,0); bvh_tree.rs:148-154 is a*m0 + b*m1)
-//   LBVH bounds: tight AABB with min seeded f32::MAX and max seeded 0 (bvh_tree.rs:42,59),
-//             size = max - min, s2 = max(w,h)^2 as main.rs:371 computes it.
-template <bool LBVH>
-__global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ meta, TreeArrays T,
-                                                           const float4 *__restrict__ sbody) {
-  if (meta->error) return;
-  const uint32_t n_nodes = meta->n_nodes;
-  for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < n_nodes; node += gridDim.x * blockDim.x) {
-    uint4 l = T.link(node);
-    if (!(l.z & kLeafBit)) continue;
-    const uint32_t s = l.y, k = l.z & kCountMask;
-    float ax = 0.f, ay = 0.f;
-    uint32_t mass = 0;
-    float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
-    for (uint32_t j = 0; j < k; ++j) {
-      const float4 b = sbody[s + j];
-      ax = __fadd_rn(ax, b.x);
-      ay = __fadd_rn(ay, b.y);
-      mass += __float_as_uint(b.w);
-      if (LBVH) {
-        mnx = mnx < b.x ? mnx : b.x; // minps
-        mny = mny < b.y ? mny : b.y;
-        mxx = mxx > b.x ? mxx : b.x; // maxps
-        mxy = mxy > b.y ? mxy : b.y;
-      }
+      for (uint32_t j = 0; j < k; ++j) place(j, order[s + j]);
     }
     const float kf = (float)k;
-    float cx = __fdiv_rn(ax, kf), cy = __fdiv_rn(ay, kf);
+    float cx = __fdiv_rn(A.ax, kf), cy = __fdiv_rn(A.ay, kf);
     float s2;
     if (LBVH) {
-      const float w = __fsub_rn(mxx, mnx), h = __fsub_rn(mxy, mny);
+      const float w = __fsub_rn(A.mxx, A.mnx), h = __fsub_rn(A.mxy, A.mny);
       const float tx = w > h ? w : h, ty = h > w ? h : w;
       s2 = __fmul_rn(tx, ty);
-      T.box[node] = make_float4(mnx, mny, __fadd_rn(mnx, w), __fadd_rn(mny, h));
-      T.bmax[node] = make_float2(mxx, mxy);
+      T.box[node] = make_float4(A.mnx, A.mny, __fadd_rn(A.mnx, w), __fadd_rn(A.mny, h));
+      T.bmax[node] = make_float2(A.mxx, A.mxy);
     } else {
       s2 = T.cm(node).w;
     }
-    T.cm(node) = make_float4(cx, cy, (float)mass, s2);
-    T.mass[node] = mass;
+    T.cm(node) = make_float4(cx, cy, (float)A.mass, s2);
+    T.mass[node] = A.mass;
 
-    uint32_t cur = node, cur_count = k, parent = l.w;
+    uint32_t cur_count = k, parent = l.w;
     while (parent != 0xffffffffu) {
       __threadfence();
       const uint32_t old = atomicAdd(&T.arrive[parent], cur_count);
@@ -371,7 +383,7 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ me
       uint32_t pm = 0;
       float bx = 0.f, by = 0.f;
       bool first = true;
-      mnx = 3.402823466e+38f; mny = 3.402823466e+38f; mxx = 0.f; mxy = 0.f;
+      float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
       for (uint32_t c = parent + 1; c < lp.x;) {
         const uint32_t cm_u = __ldcg(&T.mass[c]);
         const float4 ccm = __ldcg(&T.cm(c));
@@ -410,11 +422,9 @@ __global__ void __launch_bounds__(128) tree_upsweep_kernel(Meta *__restrict__ me
         const float ex = 0.01f * (pb.z - pb.x), ey = 0.01f * (pb.w - pb.y);
         if (!(cx >= pb.x - ex && cx <= pb.z + ex && cy >= pb.y - ey && cy <= pb.w + ey)) meta->cog_outside = 1u;
       }
-      cur = parent;
       cur_count = total;
       parent = lp.w;
     }
-    (void)cur;
   }
 }
 
