@@ -44,28 +44,6 @@ constexpr uint32_t kLeafBit = 0x80000000u;
 constexpr uint32_t kTwigBit = 0x40000000u; // internal node whose children are all leaves
 constexpr uint32_t kCountMask = 0x3fffffffu;
 
-__global__ void tree_prepare_kernel(const unsigned long long *__restrict__ skeys, uint32_t n, int quad_mode,
-                                    Meta *meta) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  uint32_t n_in = n;
-  if (quad_mode) { // first sorted position holding kKeyOut
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-      uint32_t mid = (lo + hi) >> 1;
-      if (skeys[mid] < kKeyOut) lo = mid + 1;
-      else hi = mid;
-    }
-    n_in = lo;
-  }
-  meta->n = n;
-  meta->n_in = n_in;
-  meta->n_nodes = 0;
-  meta->n_leaves = 0;
-  meta->max_depth = 0;
-  meta->overflow_leaves = 0;
-  meta->cog_outside = 0;
-}
-
 // smallest j in (i, hi) whose depth-d prefix differs from k[i]'s; hi if none.  Gallop + bisect.
 template <int BPL>
 __device__ __forceinline__ uint32_t find_end(const unsigned long long *__restrict__ skeys, uint32_t i,
