@@ -229,6 +229,16 @@ class World:
         self._ck(self._L.nb_draw(self._ctx, frame.ctypes.data, render_h))
         return frame
 
+    def save(self, path, steps_done=0):
+        self._ck(self._L.nb_save_snapshot(self._ctx, str(path).encode(), int(steps_done)))
+
+    def load(self, path):
+        sd = C.c_uint64(0)
+        self._ck(self._L.nb_load_snapshot(self._ctx, str(path).encode(), C.byref(sd)))
+        info_n = np.fromfile(str(path), dtype="<u8", count=3)[2]
+        self.n = int(info_n)
+        return sd.value
+
     # ---- multi-GPU ---------------------------------------------------------------------------
     @staticmethod
     def comm_unique_id():

@@ -139,6 +139,8 @@ def load(path=LIB_PATH):
         "nb_get_tree_info": (C.c_int, [vp, P(NbTreeInfo)]),
         "nb_get_tree": (C.c_int, [vp, P(NbTreeView)]),
         "nb_draw": (C.c_int, [vp, vp, C.c_uint32]),
+        "nb_save_snapshot": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
+        "nb_load_snapshot": (C.c_int, [vp, C.c_char_p, P(C.c_uint64)]),
         "nb_comm_unique_id": (C.c_int, [vp]),
         "nb_comm_init": (C.c_int, [vp, C.c_int, C.c_int, vp]),
         "nb_comm_owned_range": (C.c_int, [vp, P(C.c_uint64), P(C.c_uint64)]),

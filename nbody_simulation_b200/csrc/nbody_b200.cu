@@ -194,7 +194,8 @@ int enqueue_build(nb_ctx *c) {
 // [first, first+count).
 int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   if (count == 0) return NB_OK;
-  static const int tpb = getenv("NB_TRAVERSE_TPB") ? atoi(getenv("NB_TRAVERSE_TPB")) : 256;
+  const int tpb = 256; // 64 / 128 measured slower (0.84 / 0.83 vs 0.80 ms at 1M); persistent warps with a
+                       // global work ticket also measured slower (0.84 ms: consecutive groups lose their shared L1)
   const uint32_t blocks = cdiv(cdiv(count, 32), (uint32_t)tpb / 32u);
   g_launches += 1;
 #define NB_TRAVERSE(EX, CNT)                                                                                  \
@@ -825,6 +826,42 @@ int nb_draw(nb_ctx *c, uint8_t *frame, uint32_t render_h) {
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
   cudaFree(buf); cudaFree(slot_of); cudaFree(dframe);
   return NB_OK;
+}
+
+// ---- snapshot ---------------------------------------------------------------------------------
+int nb_save_snapshot(nb_ctx *c, const char *path, uint64_t steps_done) {
+  if (!c || !path) return NB_ERR_INVALID;
+  std::vector<nb_particle> buf(c->n);
+  int rc = nb_get_bodies_aos(c, buf.data(), buf.size());
+  if (rc != NB_OK) return rc;
+  FILE *f = fopen(path, "wb");
+  if (!f) return fail(c, NB_ERR_INVALID, std::string("cannot open ") + path);
+  const char magic[8] = {'N', 'B', 'B', '2', 'S', 'N', 'A', 'P'};
+  const uint32_t ver[2] = {1u, 0u};
+  const uint64_t hdr[2] = {(uint64_t)c->n, steps_done};
+  bool ok = fwrite(magic, 1, 8, f) == 8 && fwrite(ver, 4, 2, f) == 2 && fwrite(hdr, 8, 2, f) == 2 &&
+            fwrite(buf.data(), sizeof(nb_particle), buf.size(), f) == buf.size();
+  ok = (fclose(f) == 0) && ok;
+  return ok ? NB_OK : fail(c, NB_ERR_INVALID, std::string("short write to ") + path);
+}
+
+int nb_load_snapshot(nb_ctx *c, const char *path, uint64_t *steps_done) {
+  if (!c || !path) return NB_ERR_INVALID;
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, NB_ERR_INVALID, std::string("cannot open ") + path);
+  char magic[8];
+  uint32_t ver[2];
+  uint64_t hdr[2];
+  bool ok = fread(magic, 1, 8, f) == 8 && fread(ver, 4, 2, f) == 2 && fread(hdr, 8, 2, f) == 2 &&
+            std::memcmp(magic, "NBB2SNAP", 8) == 0 && ver[0] == 1u;
+  if (!ok) { fclose(f); return fail(c, NB_ERR_INVALID, std::string("not a snapshot: ") + path); }
+  if (hdr[0] > c->cfg.n_max) { fclose(f); return fail(c, NB_ERR_CAPACITY, "snapshot holds more bodies than n_max"); }
+  std::vector<nb_particle> buf(hdr[0]);
+  ok = fread(buf.data(), sizeof(nb_particle), buf.size(), f) == buf.size();
+  fclose(f);
+  if (!ok) return fail(c, NB_ERR_INVALID, std::string("truncated snapshot: ") + path);
+  if (steps_done) *steps_done = hdr[1];
+  return nb_set_bodies_aos(c, buf.data(), buf.size());
 }
 
 // ---- multi-GPU -------------------------------------------------------------------------------

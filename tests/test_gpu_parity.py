@@ -222,6 +222,21 @@ def test_lbvh_auto_domain():
     w.close()
 
 
+def test_snapshot_resume_is_bit_identical(tmp_path):
+    p = scene("galaxy", 30_000)
+    a = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    a.set_particles(p)
+    a.step(3)
+    a.save(tmp_path / "s.nbb", 3)
+    a.step(2)
+    b = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    assert b.load(tmp_path / "s.nbb") == 3
+    b.step(2)
+    assert np.array_equal(bits(a.particles), bits(b.particles))
+    a.close()
+    b.close()
+
+
 def test_draw_matches_sequential_reference():
     p = scene("default", 0)
     w = nb.World(len(p))
