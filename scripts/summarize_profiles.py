@@ -19,6 +19,8 @@ lines = [l for l in open(path) if not l.startswith("==")]
 agg = collections.OrderedDict()
 for row in csv.DictReader(lines):
     k = row["Kernel Name"].split("(")[0].replace("void ", "").replace("nb::", "")
+    if k.startswith("fp32_ubench_kernel"):
+        continue  # roofline-denominator microbenchmarks bench.py runs after the timed region: not part of a step
     agg.setdefault(k, []).append(float(row["Metric Value"].replace(",", "")))
 tot = sum(sum(v) for v in agg.values())
 with open(os.path.join(out_dir, f"{tag}_launches.md"), "w") as f:
