@@ -16,7 +16,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (NB_FORCE_EXACT, NB_FORCE_FAST, NB_SCENE_DEFAULT, NB_SCENE_PLUMMER,
-                   NB_SCENE_TWO_GALAXY, NB_SCENE_UNIFORM_DISC, NB_TREE_LBVH, NB_TREE_QUAD,
+                   NB_SCENE_TWO_GALAXY, NB_SCENE_UNIFORM_DISC, NB_TREE_BVH_REF, NB_TREE_LBVH, NB_TREE_QUAD,
                    PARTICLE_DTYPE, NbConfig, NbCounting, NbTreeInfo)
 
 HEIGHT = 100_000        # src/main.rs:31

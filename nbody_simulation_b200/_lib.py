@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
 
 NB_OK, NB_ERR_INVALID, NB_ERR_CUDA, NB_ERR_CAPACITY, NB_ERR_NCCL, NB_ERR_OVERFLOW = range(6)
-NB_TREE_QUAD, NB_TREE_LBVH = 0, 1
+NB_TREE_QUAD, NB_TREE_LBVH, NB_TREE_BVH_REF = 0, 1, 2
 NB_FORCE_EXACT, NB_FORCE_FAST = 0, 1
 NB_SCENE_DEFAULT, NB_SCENE_UNIFORM_DISC, NB_SCENE_PLUMMER, NB_SCENE_TWO_GALAXY = range(4)
 NB_UNIQUE_ID_BYTES = 128

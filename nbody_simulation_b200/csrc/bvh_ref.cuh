@@ -1,0 +1,458 @@
+// bvh_ref.cuh — NB_TREE_BVH_REF: the reference's LIVE tree, BVHTree::from (src/bvh_tree.rs:57-96),
+// built level-synchronously on the device with the reference's exact topology and body order.
+//
+// BVHTree::from is a serial top-down recursion: fold (min, max, sum) over the slice, mean = sum/len,
+// count bodies above the mean on each axis, pick the axis whose count is closer to len/2
+// (`vert > hori` -> x), `partition` the slice in place (predicate-true side first), recurse while a side
+// holds > 64 bodies.  Everything in it is order-independent EXCEPT
+//   (1) the f32 `sum` fold (bvh_tree.rs:58-61) — evaluated here bit-exactly in parallel, seqfold_core.h;
+//   (2) the in-place `partition` (crate partition 0.1.2, two-pointer swap): the k-th predicate-false body
+//       from the left of the true zone is swapped with the k-th predicate-true body from the right of the
+//       false zone — ranks from one device-wide prefix sum of the predicate flags per level.
+// One level of the tree = all nodes of that depth at once:
+//   fold (small: one warp per node, big: one block per node and axis) -> count -> decide (children,
+//   next level's lists) -> flag scan -> publish misplaced trues -> swap.
+// Nodes live in a breadth-first pool; afterwards subtree sizes (atomic bottom-up) give every node its
+// depth-first pre-order index and the tree is emitted into the TreeArrays the up-sweep and the
+// traversal already use.
+#pragma once
+#include "common.cuh"
+#include "scan.cuh"
+#include "seqfold_core.h"
+#include "tree_build.cuh"
+
+namespace nb {
+
+constexpr uint32_t kBvhSmall = 4096;    // fold by one warp up to this many bodies
+constexpr int kBvhMaxLevels = 96;       // the reference recurses without bound (stack overflow on
+                                        // coincident bodies); here the remaining nodes become leaves
+constexpr uint32_t kBNodeLeaf = 0x40000000u;
+constexpr uint32_t kBNodeAxisX = 0x80000000u;
+
+struct BNode { // 48 B, breadth-first pool
+  uint32_t start, len;
+  uint32_t parent;  // pool index, 0xffffffff for the root
+  uint32_t child0;  // pool index of the predicate-true child; the other is child0 + 1
+  float meanx, meany;
+  uint32_t cx, cy;  // bodies with x > mean.x / y > mean.y
+  uint32_t T;       // size of the predicate-true side
+  uint32_t flags;   // kBNodeAxisX | kBNodeLeaf | level
+  uint32_t size;    // nodes in the subtree
+  uint32_t arrive;  // children whose size is known
+};
+
+struct BvhMeta {
+  uint32_t n_nodes;
+  uint32_t overflow;                 // leaves forced at the level cap
+  uint32_t cnt_big[kBvhMaxLevels + 2];   // active nodes per level, by fold class
+  uint32_t cnt_small[kBvhMaxLevels + 2];
+  uint32_t levels;                   // levels actually built (host bookkeeping)
+};
+
+struct BvhWork {
+  BNode *nodes;
+  uint32_t node_cap;
+  uint32_t *list_big[2], *list_small[2]; // ping-pong by level parity
+  float *wx, *wy;     // positions in the current (partially partitioned) order
+  uint32_t *order;    // position -> storage slot of the body
+  uint32_t *seg;      // position -> pool index of the node that currently owns the body
+  uint32_t *F;        // exclusive prefix of predicate-false flags
+  uint32_t *listT;    // misplaced predicate-true positions, by rank from the right
+  uint32_t *bsum;
+  BvhMeta *meta;
+};
+
+// ---- init: copy positions into the working arrays, root node --------------------------------------
+__global__ void __launch_bounds__(256) bvh_init_kernel(BvhWork W, Meta *meta, const float *__restrict__ x,
+                                                       const float *__restrict__ y, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    W.wx[i] = x[i];
+    W.wy[i] = y[i];
+    W.order[i] = i;
+    W.seg[i] = 0;
+  }
+  if (i == 0) {
+    BNode r{};
+    r.start = 0;
+    r.len = n;
+    r.parent = 0xffffffffu;
+    r.flags = 0; // level 0; always a Root (bvh_tree.rs:90), even with <= 64 bodies
+    W.nodes[0] = r;
+    BvhMeta *m = W.meta;
+    m->n_nodes = 1;
+    m->overflow = 0;
+    for (int l = 0; l < kBvhMaxLevels + 2; ++l) m->cnt_big[l] = m->cnt_small[l] = 0;
+    meta->n = n; // per-step metadata (the Morton pipeline initialises it in its sort)
+    meta->n_in = n;
+    meta->n_nodes = 0;
+    meta->n_leaves = 0;
+    meta->max_depth = 0;
+    meta->overflow_leaves = 0;
+    meta->cog_outside = 0;
+    if (n > kBvhSmall) { m->cnt_big[0] = 1; W.list_big[0][0] = 0; }
+    else { m->cnt_small[0] = 1; W.list_small[0][0] = 0; }
+  }
+}
+
+// ---- fold, small nodes: one warp per node, both axes, literally sequential ---------------------------
+__global__ void __launch_bounds__(256) bvh_fold_small_kernel(BvhWork W, int level) {
+  const uint32_t cnt = W.meta->cnt_small[level];
+  const uint32_t *list = W.list_small[level & 1];
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t a = warp; a < cnt; a += nwarps) {
+    const uint32_t ni = list[a];
+    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
+    float ax = 0.f, ay = 0.f;
+    for (uint32_t base = 0; base < len; base += 32) {
+      const uint32_t c = min(32u, len - base);
+      const float vx = lane < c ? W.wx[s + base + lane] : 0.f;
+      const float vy = lane < c ? W.wy[s + base + lane] : 0.f;
+      if (c == 32) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
+          ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
+        }
+      } else {
+        for (uint32_t j = 0; j < c; ++j) {
+          ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
+          ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
+        }
+      }
+    }
+    if (lane == 0) {
+      const float lf = __uint2float_rn(len); // `points.len() as f32`, bvh_tree.rs:67
+      W.nodes[ni].meanx = __fdiv_rn(ax, lf);
+      W.nodes[ni].meany = __fdiv_rn(ay, lf);
+      W.nodes[ni].cx = 0;
+      W.nodes[ni].cy = 0;
+    }
+  }
+}
+
+// ---- fold, big nodes: one 1024-thread block per (node, axis), windows of 8192 addends ------------------
+constexpr int kFoldThreads = 1024;
+constexpr int kFoldChunk = 8;
+constexpr int kFoldWindow = kFoldThreads * kFoldChunk;
+
+__device__ __forceinline__ sf::Summary shfl_up_summary(const sf::Summary &s, int o) {
+  sf::Summary t;
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    t.tot[p] = __shfl_up_sync(0xffffffffu, s.tot[p], o);
+    t.lo[p] = __shfl_up_sync(0xffffffffu, s.lo[p], o);
+    t.hi[p] = __shfl_up_sync(0xffffffffu, s.hi[p], o);
+  }
+  return t;
+}
+
+// Exact sequential f32 sum of x[0..len) evaluated by the whole block (see seqfold_core.h).
+__device__ float block_seqfold(const float *__restrict__ x, uint32_t len) {
+  __shared__ float sx[kFoldWindow + kFoldWindow / 32];
+  __shared__ sf::Summary wsum[kFoldThreads / 32];
+  __shared__ float acc_s;
+  __shared__ uint32_t pos_s;
+  const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (tid == 0) { acc_s = 0.f; pos_s = 0; }
+  __syncthreads();
+  for (;;) {
+    const float acc = acc_s;
+    const uint32_t pos = pos_s;
+    if (pos >= len) return acc;
+    sf::Binade b;
+    if (!sf::binade_of(acc, b)) { // zero / subnormal / non-finite accumulator: one plain step
+      __syncthreads();
+      if (tid == 0) { acc_s = __fadd_rn(acc, x[pos]); pos_s = pos + 1; }
+      __syncthreads();
+      continue;
+    }
+    const uint32_t wlen = min((uint32_t)kFoldWindow, len - pos);
+    for (uint32_t i = tid; i < wlen; i += kFoldThreads) sx[i + (i >> 5)] = x[pos + i];
+    __syncthreads();
+    const uint32_t c0 = tid * kFoldChunk;
+    sf::Summary own = sf::identity();
+#pragma unroll
+    for (int j = 0; j < kFoldChunk; ++j) {
+      const uint32_t i = c0 + j;
+      if (i < wlen) sf::push(own, sf::quantize(sx[i + (i >> 5)], b));
+    }
+    // inclusive scan of the chunk functions in sequence order
+    sf::Summary inc = own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const sf::Summary t = shfl_up_summary(inc, o);
+      if (lane >= (unsigned)o) inc = sf::compose(t, inc);
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+      sf::Summary v = wsum[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const sf::Summary t = shfl_up_summary(v, o);
+        if (lane >= (unsigned)o) v = sf::compose(t, v);
+      }
+      wsum[lane] = v; // inclusive over warps
+    }
+    __syncthreads();
+    sf::Summary pre = shfl_up_summary(inc, 1); // exclusive within the warp
+    if (lane == 0) pre = sf::identity();
+    if (w > 0) pre = sf::compose(wsum[w - 1], pre);
+    const int p0 = b.A & 1;
+    const bool prefix_ok = sf::valid_from(pre, b.A);
+    const int32_t Ain = b.A + pre.tot[p0];
+    const bool bad = prefix_ok && !sf::valid_from(own, Ain);
+    const int any_bad = __syncthreads_or(bad);
+    if (!any_bad) {
+      if (tid == kFoldThreads - 1) {
+        const sf::Summary all = wsum[kFoldThreads / 32 - 1];
+        acc_s = sf::binade_value(b, b.A + all.tot[p0]);
+        pos_s = pos + wlen;
+      }
+    } else if (bad) { // the first chunk in which the accumulator leaves the binade: walk it
+      int32_t Ar = Ain;
+      for (int j = 0; j < kFoldChunk; ++j) {
+        const uint32_t i = c0 + j;
+        const float xv = sx[i + (i >> 5)];
+        const sf::QElem q = sf::quantize(xv, b);
+        if (!sf::step_valid(q, Ar)) {
+          acc_s = __fadd_rn(sf::binade_value(b, Ar), xv);
+          pos_s = pos + i + 1;
+          break;
+        }
+        Ar = sf::step_apply(q, Ar);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kFoldThreads) bvh_fold_big_kernel(BvhWork W, int level) {
+  const uint32_t cnt = W.meta->cnt_big[level];
+  const uint32_t *list = W.list_big[level & 1];
+  const bool ydim = blockIdx.y != 0;
+  for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
+    const uint32_t ni = list[a];
+    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
+    const float sum = block_seqfold((ydim ? W.wy : W.wx) + s, len);
+    if (threadIdx.x == 0) {
+      const float mean = __fdiv_rn(sum, __uint2float_rn(len));
+      if (ydim) { W.nodes[ni].meany = mean; W.nodes[ni].cy = 0; }
+      else { W.nodes[ni].meanx = mean; W.nodes[ni].cx = 0; }
+    }
+    __syncthreads();
+  }
+}
+
+// A body's node is split at this level?
+__device__ __forceinline__ bool bvh_active(const BNode &nd, int level) {
+  return nd.flags == (uint32_t)level || nd.flags == ((uint32_t)level | kBNodeAxisX);
+}
+
+// ---- count: bodies above the mean on each axis (bvh_tree.rs:70-72) -----------------------------------
+__global__ void __launch_bounds__(256) bvh_count_kernel(BvhWork W, uint32_t n, int level) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31;
+  uint32_t ni = 0xffffffffu;
+  bool gx = false, gy = false;
+  if (i < n) {
+    ni = W.seg[i];
+    const BNode &nd = W.nodes[ni];
+    if (nd.flags == (uint32_t)level) {
+      gx = W.wx[i] > nd.meanx;
+      gy = W.wy[i] > nd.meany;
+    } else ni = 0xffffffffu;
+  }
+  // bodies of a node are contiguous: almost every warp holds one node
+  const uint32_t first = __shfl_sync(0xffffffffu, ni, 0);
+  if (__all_sync(0xffffffffu, ni == first)) {
+    if (first == 0xffffffffu) return;
+    const uint32_t bx = __popc(__ballot_sync(0xffffffffu, gx)), by = __popc(__ballot_sync(0xffffffffu, gy));
+    if (lane == 0) {
+      if (bx) atomicAdd(&W.nodes[first].cx, bx);
+      if (by) atomicAdd(&W.nodes[first].cy, by);
+    }
+  } else if (ni != 0xffffffffu) {
+    if (gx) atomicAdd(&W.nodes[ni].cx, 1u);
+    if (gy) atomicAdd(&W.nodes[ni].cy, 1u);
+  }
+}
+
+// ---- decide: axis, split point, children, next level's lists (bvh_tree.rs:69-88) -------------------------
+__global__ void __launch_bounds__(256) bvh_decide_kernel(BvhWork W, int level, uint32_t target) {
+  BvhMeta *m = W.meta;
+  const uint32_t nb = m->cnt_big[level], ns = m->cnt_small[level];
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= nb + ns) return;
+  const uint32_t ni = a < nb ? W.list_big[level & 1][a] : W.list_small[level & 1][a - nb];
+  BNode &nd = W.nodes[ni];
+  const uint32_t len = nd.len, half = len / 2;
+  const uint32_t hori = half > nd.cx ? half - nd.cx : nd.cx - half; // abs_diff, bvh_tree.rs:71
+  const uint32_t vert = half > nd.cy ? half - nd.cy : nd.cy - half;
+  const bool xaxis = vert > hori;                                   // bvh_tree.rs:73
+  const uint32_t T = xaxis ? nd.cx : nd.cy;
+  const uint32_t c0 = atomicAdd(&m->n_nodes, 2u);
+  nd.T = T;
+  nd.flags = (uint32_t)level | (xaxis ? kBNodeAxisX : 0u);
+  if (c0 + 2 > W.node_cap) { nd.child0 = 0; return; } // pool exhausted: reported by the emit kernel
+  nd.child0 = c0;
+  for (int k = 0; k < 2; ++k) {
+    BNode ch{};
+    ch.start = nd.start + (k ? T : 0u);
+    ch.len = k ? len - T : T;
+    ch.parent = ni;
+    const bool internal = ch.len > target; // TARGET_POINTS, bvh_tree.rs:37,78,84
+    if (internal && level + 1 < kBvhMaxLevels) {
+      ch.flags = (uint32_t)(level + 1);
+      if (ch.len > kBvhSmall) W.list_big[(level + 1) & 1][atomicAdd(&m->cnt_big[level + 1], 1u)] = c0 + k;
+      else W.list_small[(level + 1) & 1][atomicAdd(&m->cnt_small[level + 1], 1u)] = c0 + k;
+    } else {
+      ch.flags = (uint32_t)(level + 1) | kBNodeLeaf;
+      ch.size = 1;
+      if (internal) atomicAdd(&m->overflow, 1u);
+    }
+    W.nodes[c0 + k] = ch;
+  }
+}
+
+// predicate-false flag of position i at this level (0 for bodies whose node is not being split)
+__device__ __forceinline__ uint32_t bvh_false_flag(const BvhWork &W, uint32_t i, int level) {
+  const BNode &nd = W.nodes[W.seg[i]];
+  if ((nd.flags & ~kBNodeAxisX) != (uint32_t)level) return 0u;
+  const bool pred = (nd.flags & kBNodeAxisX) ? (W.wx[i] > nd.meanx) : (W.wy[i] > nd.meany);
+  return pred ? 0u : 1u;
+}
+
+// ---- device-wide exclusive scan of the predicate-false flags (flags evaluated on the fly) --------------
+__global__ void __launch_bounds__(kScanThreads) bvh_flag_reduce_kernel(BvhWork W, uint32_t n, int level) {
+  const uint32_t i0 = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+  uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k)
+    if (i0 + k < n) s += bvh_false_flag(W, i0 + k, level);
+  uint32_t tot;
+  block_exclusive_scan<kScanThreads>(s, tot);
+  if (threadIdx.x == 0) W.bsum[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(kScanThreads) bvh_flag_apply_kernel(BvhWork W, uint32_t n, int level) {
+  const uint32_t i0 = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+  uint32_t v[kScanItems], s = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    v[k] = (i0 + k < n) ? bvh_false_flag(W, i0 + k, level) : 0u;
+    s += v[k];
+  }
+  uint32_t tot;
+  uint32_t ex = block_exclusive_scan<kScanThreads>(s, tot) + W.bsum[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    if (i0 + k < n) W.F[i0 + k] = ex;
+    ex += v[k];
+  }
+}
+
+// ---- partition (crate `partition`, bvh_tree.rs:74-76): publish, then swap -------------------------------
+// A predicate-true body at position j >= start+T is misplaced; its rank from the right is the number of
+// predicate-true bodies after it.  The two-pointer loop swaps it with the misplaced false of equal rank
+// from the left.
+__global__ void __launch_bounds__(256) bvh_publish_kernel(BvhWork W, uint32_t n, int level) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const BNode &nd = W.nodes[W.seg[i]];
+  if ((nd.flags & ~kBNodeAxisX) != (uint32_t)level) return;
+  const uint32_t s = nd.start, T = nd.T;
+  if (i < s + T) return;
+  const bool pred = (nd.flags & kBNodeAxisX) ? (W.wx[i] > nd.meanx) : (W.wy[i] > nd.meany);
+  if (!pred) return;
+  const uint32_t fb = W.F[i] - W.F[s];     // falses before i inside the node
+  const uint32_t tb = (i - s) - fb;        // trues before i
+  W.listT[s + (T - tb - 1u)] = i;
+}
+__global__ void __launch_bounds__(256) bvh_swap_kernel(BvhWork W, uint32_t n, int level) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t ni = W.seg[i];
+  const BNode &nd = W.nodes[ni];
+  if ((nd.flags & ~kBNodeAxisX) != (uint32_t)level) return;
+  const uint32_t s = nd.start, T = nd.T;
+  W.seg[i] = nd.child0 + (i < s + T ? 0u : 1u);
+  if (i >= s + T) return;
+  const float xi = W.wx[i], yi = W.wy[i];
+  const bool pred = (nd.flags & kBNodeAxisX) ? (xi > nd.meanx) : (yi > nd.meany);
+  if (pred) return;
+  const uint32_t j = W.listT[s + (W.F[i] - W.F[s])]; // partner: misplaced true of the same rank
+  const uint32_t oi = W.order[i];
+  W.wx[i] = W.wx[j]; W.wy[i] = W.wy[j]; W.order[i] = W.order[j];
+  W.wx[j] = xi; W.wy[j] = yi; W.order[j] = oi;
+}
+
+// ---- subtree sizes, atomic bottom-up -----------------------------------------------------------------
+__global__ void __launch_bounds__(256) bvh_sizes_kernel(BvhWork W) {
+  const uint32_t nn = min(W.meta->n_nodes, W.node_cap);
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nn; v += gridDim.x * blockDim.x) {
+    if (!(W.nodes[v].flags & kBNodeLeaf)) continue;
+    uint32_t p = W.nodes[v].parent;
+    while (p != 0xffffffffu) {
+      __threadfence();
+      if (atomicAdd(&W.nodes[p].arrive, 1u) == 0u) break; // the second child to arrive owns the parent
+      __threadfence();
+      const uint32_t c0 = W.nodes[p].child0;
+      const uint32_t sz = 1u + __ldcg(&W.nodes[c0].size) + __ldcg(&W.nodes[c0 + 1].size);
+      W.nodes[p].size = sz;
+      p = W.nodes[p].parent;
+    }
+  }
+}
+
+// ---- pre-order index by climbing to the root, then emit into the traversal's arrays ------------------
+// order[] (position -> storage slot) is what the finish kernel gathers through.
+__global__ void __launch_bounds__(256) bvh_emit_kernel(BvhWork W, Meta *meta, TreeArrays T, uint32_t n) {
+  const uint32_t nn = W.meta->n_nodes;
+  if (nn > W.node_cap || nn > T.capacity) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) { meta->error |= 1u; meta->n_nodes = nn; }
+    return;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    meta->n_nodes = nn;
+    meta->n_in = n;
+    meta->overflow_leaves = W.meta->overflow;
+  }
+  uint32_t leaves = 0, maxd = 0;
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nn; v += gridDim.x * blockDim.x) {
+    const BNode nd = W.nodes[v];
+    uint32_t pre = 0, c = v, p = nd.parent, parent_pre = 0xffffffffu;
+    bool first = true;
+    uint32_t up = 0; // offset of v from its parent in pre-order
+    while (p != 0xffffffffu) {
+      const uint32_t pc0 = W.nodes[p].child0;
+      const uint32_t off = 1u + (c == pc0 ? 0u : W.nodes[pc0].size);
+      if (first) { up = off; first = false; }
+      pre += off;
+      c = p;
+      p = W.nodes[p].parent;
+    }
+    if (nd.parent != 0xffffffffu) parent_pre = pre - up;
+    const bool leaf = (nd.flags & kBNodeLeaf) != 0;
+    uint32_t z = nd.len | (leaf ? kLeafBit : 0u);
+    if (!leaf) {
+      const uint32_t f0 = W.nodes[nd.child0].flags, f1 = W.nodes[nd.child0 + 1].flags;
+      if ((f0 & kBNodeLeaf) && (f1 & kBNodeLeaf)) z |= kTwigBit;
+    }
+    const uint32_t lvl = nd.flags & 0xffffu;
+    T.depth[pre] = (int32_t)lvl;
+    T.link(pre) = make_uint4(pre + nd.size, nd.start, z, parent_pre);
+    T.arrive[pre] = 0;
+    leaves += leaf ? 1u : 0u;
+    maxd = max(maxd, lvl);
+  }
+  leaves = __reduce_add_sync(0xffffffffu, leaves);
+  maxd = __reduce_max_sync(0xffffffffu, maxd);
+  if ((threadIdx.x & 31) == 0) {
+    if (leaves) atomicAdd(&meta->n_leaves, leaves);
+    if (maxd) atomicMax(&meta->max_depth, maxd);
+  }
+}
+
+} // namespace nb

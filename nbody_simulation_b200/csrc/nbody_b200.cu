@@ -24,6 +24,7 @@
 #include "traverse.cuh"
 #include "ubench.cuh"
 #include "tree_build.cuh"
+#include "bvh_ref.cuh"
 
 using namespace nb;
 
@@ -84,6 +85,10 @@ struct nb_ctx {
   uint32_t n_alloc = 0; // array capacity (padded)
   int leaf_cap = 8;
   bool quad = true;
+  bool bvh_ref = false;   // NB_TREE_BVH_REF: level-synchronous BVHTree::from (bvh_ref.cuh)
+  BvhWork bw{};
+  BvhMeta *h_bmeta = nullptr; // pinned mirror of bw.meta
+  uint32_t bvh_levels = 0;    // levels of the last build
 
   BodyArrays body[2]{};
   int cur = 0; // body[cur] holds the current state (slot order)
@@ -159,11 +164,53 @@ void owned_range(const nb_ctx *c, uint32_t &first, uint32_t &count) {
 
 // ---- one build: morton -> sort -> topology -> up-sweep (BVHTree::from + calculate_gravity,
 // bvh_tree.rs:57-158 / QuadTree::insert + calculate_gravity, quad_tree.rs:153-270) --------------
+// NB_TREE_BVH_REF: BVHTree::from (bvh_tree.rs:57-96) level by level, then the shared up-sweep.
+int enqueue_build_bvh_ref(nb_ctx *c) {
+  const uint32_t n = c->n;
+  cudaStream_t st = c->stream;
+  BodyArrays &b = c->body[c->cur];
+  BvhWork &W = c->bw;
+  const unsigned long long l0 = g_launches;
+  bvh_init_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, c->meta, b.x, b.y, n);
+  g_launches += 1;
+  const uint32_t scan_blocks = cdiv(n, (uint32_t)kScanTile);
+  int level = 0;
+  for (; level < kBvhMaxLevels; ++level) {
+    NB_CUDA(c, cudaMemcpyAsync(c->h_bmeta, W.meta, sizeof(BvhMeta), cudaMemcpyDeviceToHost, st));
+    NB_CUDA(c, cudaStreamSynchronize(st));
+    const uint32_t nbig = c->h_bmeta->cnt_big[level], nsmall = c->h_bmeta->cnt_small[level];
+    if (nbig + nsmall == 0) break;
+    if (c->h_bmeta->n_nodes + 2 * (nbig + nsmall) > W.node_cap)
+      return fail(c, NB_ERR_OVERFLOW, "BVH node pool too small");
+    if (nsmall) bvh_fold_small_kernel<<<std::min(cdiv(nsmall, 8u), (uint32_t)kSMs * 8u), 256, 0, st>>>(W, level);
+    if (nbig) bvh_fold_big_kernel<<<dim3(std::min(nbig, (uint32_t)kSMs * 2u), 2), kFoldThreads, 0, st>>>(W, level);
+    bvh_count_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
+    bvh_decide_kernel<<<cdiv(nbig + nsmall, 256), 256, 0, st>>>(W, level, (uint32_t)c->leaf_cap);
+    bvh_flag_reduce_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
+    scan_bsum_kernel<<<1, 1024, 0, st>>>(W.bsum, scan_blocks, nullptr);
+    bvh_flag_apply_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
+    bvh_publish_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
+    bvh_swap_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
+    g_launches += 7 + (nsmall ? 1 : 0) + (nbig ? 1 : 0);
+  }
+  c->bvh_levels = (uint32_t)level;
+  bvh_sizes_kernel<<<kSMs * 8, 256, 0, st>>>(W);
+  bvh_emit_kernel<<<kSMs * 8, 256, 0, st>>>(W, c->meta, c->T, n);
+  tree_finish_kernel<true, 8, true><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, W.order, b.x, b.y, b.m, b.id, c->sbody);
+  g_launches += 3;
+  (void)l0;
+  NB_CUDA(c, cudaGetLastError());
+  c->sorted_in = 0; // the tree order lives in vals[0]
+  c->tree_valid = true;
+  return NB_OK;
+}
+
 int enqueue_build(nb_ctx *c) {
   const uint32_t n = c->n;
   cudaStream_t st = c->stream;
   BodyArrays &b = c->body[c->cur];
   if (n == 0) return NB_OK;
+  if (c->bvh_ref) return enqueue_build_bvh_ref(c);
   if (!c->quad && c->cfg.domain_auto) {
     const int np = kSMs * 4;
     g_launches += 2;
@@ -389,6 +436,9 @@ void nb_destroy(nb_ctx *c) {
   cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
   cudaFree(c->flush_buf);
   if (c->h_meta) cudaFreeHost(c->h_meta);
+  if (c->h_bmeta) cudaFreeHost(c->h_bmeta);
+  cudaFree(c->bw.nodes); cudaFree(c->bw.meta);
+  for (int i = 0; i < 2; ++i) { cudaFree(c->bw.list_big[i]); cudaFree(c->bw.list_small[i]); }
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -399,7 +449,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
     fail(nullptr, NB_ERR_INVALID, "nb_create: n_max must be in [1, 2^30)");
     return nullptr;
   }
-  if (cfg->tree_kind != NB_TREE_QUAD && cfg->tree_kind != NB_TREE_LBVH) {
+  if (cfg->tree_kind != NB_TREE_QUAD && cfg->tree_kind != NB_TREE_LBVH && cfg->tree_kind != NB_TREE_BVH_REF) {
     fail(nullptr, NB_ERR_INVALID, "nb_create: unknown tree_kind");
     return nullptr;
   }
@@ -423,7 +473,8 @@ nb_ctx *nb_create(const nb_config *cfg) {
   c->cfg = *cfg;
   c->device = cfg->device;
   c->quad = cfg->tree_kind == NB_TREE_QUAD;
-  c->leaf_cap = cfg->leaf_cap ? cfg->leaf_cap : (c->quad ? 8 : 64);
+  c->bvh_ref = cfg->tree_kind == NB_TREE_BVH_REF;
+  c->leaf_cap = cfg->leaf_cap ? cfg->leaf_cap : (c->quad ? 8 : 64); // MAX_CAPACITY / TARGET_POINTS
   if (c->cfg.domain_h <= 0.f) { c->cfg.domain_x0 = 0.f; c->cfg.domain_y0 = 0.f; c->cfg.domain_h = 100000.f; }
   auto bail = [&](const char *what, cudaError_t err) -> nb_ctx * {
     fail(nullptr, NB_ERR_CUDA, std::string("nb_create: ") + what + ": " + cudaGetErrorString(err));
@@ -462,6 +513,26 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->meta, 1));
   NB_TRY(dmalloc(&c->aos, 6 * na));
   NB_TRY(cudaMallocHost((void **)&c->h_meta, sizeof(Meta)));
+  if (c->bvh_ref) {
+    // working arrays alias the Morton pipeline's buffers, which this tree kind does not use
+    BvhWork &W = c->bw;
+    W.wx = reinterpret_cast<float *>(c->keys[0]);
+    W.wy = W.wx + na;
+    W.F = reinterpret_cast<uint32_t *>(c->keys[1]);
+    W.listT = W.F + na;
+    W.order = c->vals[0];
+    W.seg = c->nstart;
+    W.bsum = c->sort.bsum;
+    W.node_cap = (uint32_t)std::min<size_t>(na / 4 + 65536, c->T.capacity);
+    NB_TRY(dmalloc(&W.nodes, (size_t)W.node_cap));
+    const size_t lcap = na / 64 + 1024;
+    for (int i = 0; i < 2; ++i) {
+      NB_TRY(dmalloc(&W.list_big[i], lcap));
+      NB_TRY(dmalloc(&W.list_small[i], lcap));
+    }
+    NB_TRY(dmalloc(&W.meta, 1));
+    NB_TRY(cudaMallocHost((void **)&c->h_bmeta, sizeof(BvhMeta)));
+  }
   Meta m0{};
   m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;
   NB_TRY(cudaMemcpy(c->meta, &m0, sizeof(Meta), cudaMemcpyHostToDevice));
@@ -750,7 +821,8 @@ int nb_get_tree(nb_ctx *c, const nb_tree_view *v) {
   if (n == 0) return NB_OK;
   BodyArrays &b = c->body[c->cur];
   const int w = c->sorted_in;
-  if (v->keys) {
+  if (v->keys && c->bvh_ref) std::memset(v->keys, 0, (size_t)n * 8); // no Morton keys in this tree
+  if (v->keys && !c->bvh_ref) {
     // recompute the slot-order keys into the free ping-pong buffer, then to original order
     unsigned long long *tmp = nullptr;
     NB_CUDA(c, dmalloc(&tmp, (size_t)n));

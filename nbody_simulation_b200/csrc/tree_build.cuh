@@ -257,7 +257,10 @@ template <bool LBVH> struct LeafAcc {
   }
 };
 
-template <bool LBVH, int MAXK>
+// REF (NB_TREE_BVH_REF, bvh_ref.cuh): the leaf slices keep the order `partition` left them in
+// (bvh_tree.rs:40-54 borrows the slice as is) and a leaf may be EMPTY (cog = 0/0, box = (MAX, -MAX)), so
+// parents are completed by counting arrived children, not bodies.
+template <bool LBVH, int MAXK, bool REF = false>
 __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ meta, TreeArrays T,
                                                           uint32_t *__restrict__ order, const float *__restrict__ x,
                                                           const float *__restrict__ y, const uint32_t *__restrict__ m,
@@ -284,7 +287,9 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
       sbody[s + j] = make_float4(bx, by, (float)mm, __uint_as_float(mm));
       A.add(bx, by, mm);
     };
-    if (k <= (uint32_t)MAXK) { // registers: bubble network, padding keys sort to the end
+    if (REF) {
+      for (uint32_t j = 0; j < k; ++j) place(j, order[s + j]);
+    } else if (k <= (uint32_t)MAXK) { // registers: bubble network, padding keys sort to the end
       uint32_t slot[MAXK], bid[MAXK];
 #pragma unroll
       for (int j = 0; j < MAXK; ++j) {
@@ -353,10 +358,10 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
     uint32_t cur_count = k, parent = l.w;
     while (parent != 0xffffffffu) {
       __threadfence();
-      const uint32_t old = atomicAdd(&T.arrive[parent], cur_count);
+      const uint32_t old = atomicAdd(&T.arrive[parent], REF ? 1u : cur_count);
       const uint4 lp = T.link(parent);
       const uint32_t total = lp.z & kCountMask;
-      if (old + cur_count != total) break;
+      if (REF ? (old != 1u) : (old + cur_count != total)) break;
       __threadfence();
       uint32_t pm = 0;
       float bx = 0.f, by = 0.f;

@@ -1,0 +1,112 @@
+"""GPU parity for NB_TREE_BVH_REF: the device build of the reference's LIVE tree, BVHTree::from
+(src/bvh_tree.rs:57-96), against the oracle's literal restatement (oracle kind 3) — topology, body
+order, masses, centres of gravity and bounds bit-exact; exact-mode forces and multi-step trajectories
+bit-exact (the reference's Vec is permuted by every build, main.rs:400, so later steps depend on the
+exact order the partitions leave)."""
+import numpy as np
+import pytest
+
+import nbody_simulation_b200 as nb
+import oracle_binding as ob
+from test_gpu_parity import TREE_KEYS, bits, scene
+
+pytestmark = pytest.mark.gpu
+
+
+def assert_bvh_equal(g, o, what):
+    for f in ("n_nodes", "n_in_tree", "n_leaves", "max_depth", "overflow_leaves"):
+        assert getattr(g["info"], f) == getattr(o["info"], f), (what, f, getattr(g["info"], f), getattr(o["info"], f))
+    for k in TREE_KEYS:
+        if k == "keys":
+            continue  # this tree has no Morton keys
+        a, b = g[k], o[k]
+        same = np.array_equal(bits(a), bits(b))
+        if not same and a.dtype.kind == "f":  # an empty leaf's 0/0: NaN payloads differ between x86 and sm_100
+            same = np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(bits(a[~np.isnan(a)]), bits(b[~np.isnan(b)]))
+        if not same:
+            bad = np.nonzero(a != b)[0]
+            raise AssertionError(f"{what}: {k} differs at {len(bad)} of {len(a)} entries, first {bad[:5]}: "
+                                 f"gpu {a[bad[:5]]} oracle {b[bad[:5]]}")
+
+
+@pytest.mark.parametrize("sc,n", [("disc", 100_000), ("default", 0), ("plummer", 150_000), ("galaxy", 120_001),
+                                  ("disc", 1_000_000)])
+def test_bvh_ref_tree_bitexact(sc, n):
+    p = scene(sc, n)
+    w = nb.World(len(p), tree=nb.NB_TREE_BVH_REF)
+    w.set_particles(p)
+    w.build_tree()
+    g = w.tree()
+    o = ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).export()
+    assert_bvh_equal(g, o, f"{sc}/{n}")
+    w.close()
+
+
+@pytest.mark.parametrize("n", [1, 2, 64, 65, 129, 5000])
+def test_bvh_ref_small_and_edge_sizes(n):
+    # the reference always splits the root (bvh_tree.rs:90), even for <= 64 bodies; n = 1 leaves one side empty
+    p = scene("disc", max(n, 16))[:n].copy()
+    w = nb.World(len(p), tree=nb.NB_TREE_BVH_REF)
+    w.set_particles(p)
+    w.build_tree()
+    assert_bvh_equal(w.tree(), ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).export(), f"n={n}")
+    w.close()
+
+
+def test_bvh_ref_positions_off_domain_and_negative():
+    # the BVH has no domain: negative and far-away coordinates (max seeded 0, bvh_tree.rs:59; mixed-sign sums)
+    r = np.random.default_rng(3)
+    p = scene("disc", 50_000)
+    p["x"] = r.normal(0.0, 3e4, len(p)).astype(np.float32)
+    p["y"] = (r.normal(-2e5, 1e4, len(p))).astype(np.float32)
+    w = nb.World(len(p), tree=nb.NB_TREE_BVH_REF)
+    w.set_particles(p)
+    w.build_tree()
+    assert_bvh_equal(w.tree(), ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).export(), "mixed sign")
+    w.close()
+
+
+@pytest.mark.parametrize("theta", [0.5, 50.0])
+def test_bvh_ref_accel_exact_is_bit_identical(theta):
+    p = scene("default", 0)
+    w = nb.World(len(p), theta=theta, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    c = nb.Counting()
+    ax, ay = w.accel(c)
+    T = ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"])
+    rx, ry, ni, nt, _ = T.accel(theta, literal=True)  # the recursive main.rs:349-386 on the pointer tree
+    assert c.interactions == ni and c.node_tests == nt
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+def test_bvh_ref_accel_fast_within_tolerance():
+    # tolerance: normwise ||da||2/||a||2 <= 1e-5 against the literal reference tree at the same theta
+    p = scene("disc", 200_000)
+    w = nb.World(len(p), theta=0.5, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_FAST)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    rx, ry, _, _, _ = ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).accel(0.5, literal=True)
+    err = ob.normwise_err(ax, ay, rx, ry)
+    assert err <= 1e-5, err
+    w.close()
+
+
+def test_bvh_ref_trajectory_is_bit_identical_to_world_update():
+    # World::update x 6 (main.rs:388-425, identity semantics): the Vec order left by each build feeds the next
+    p = scene("default", 0)[:60_000].copy()
+    theta, dt, steps = 0.7, 0.1, 6
+    w = nb.World(len(p), theta=theta, dt=dt, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    c = nb.Counting()
+    w.step(steps, c)
+    ow = ob.OracleWorld(p)
+    oc = None
+    for _ in range(steps):
+        oc = ow.update(ob.KIND_LITERAL_BVH, dt, theta, counting=oc)
+    x, y, vx, vy, m = ow.get()
+    q = w.particles
+    assert c.interactions == oc.interactions and c.node_tests == oc.node_tests
+    for a, b in ((q["x"], x), (q["y"], y), (q["vx"], vx), (q["vy"], vy), (q["weight"], m)):
+        assert np.array_equal(bits(a), bits(b))
+    w.close()
