@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-per-gpu", type=int, default=1_000_000)
     ap.add_argument("--scene", default="disc", choices=["disc", "plummer", "galaxy", "default"])
-    ap.add_argument("--tree", default="quad", choices=["quad", "lbvh"])
+    ap.add_argument("--tree", default="quad", choices=["quad", "lbvh", "bvhref"])
     ap.add_argument("--theta", type=float, default=0.5)
     ap.add_argument("--force", default="fast", choices=["fast", "exact"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -208,7 +208,7 @@ def main():
     n_total = args.n_per_gpu * world
     parts = make_scene(nb, args, n_total)
     n_total = len(parts)
-    tree = nb.NB_TREE_QUAD if args.tree == "quad" else nb.NB_TREE_LBVH
+    tree = {"quad": nb.NB_TREE_QUAD, "lbvh": nb.NB_TREE_LBVH, "bvhref": nb.NB_TREE_BVH_REF}[args.tree]
     force = nb.NB_FORCE_FAST if args.force == "fast" else nb.NB_FORCE_EXACT
     w = nb.World(n_total, theta=args.theta, dt=0.1, tree=tree, force_mode=force, device=local_rank)
     if world > 1:

@@ -132,10 +132,27 @@ __global__ void __launch_bounds__(256) bvh_fold_small_kernel(BvhWork W, int leve
   }
 }
 
-// ---- fold, big nodes: one 1024-thread block per (node, axis), windows of 8192 addends ------------------
-constexpr int kFoldThreads = 1024;
-constexpr int kFoldChunk = 8;
-constexpr int kFoldWindow = kFoldThreads * kFoldChunk;
+// ---- fold, big nodes -------------------------------------------------------------------------------------
+// The exact sequential sum of a long slice (seqfold_core.h) in three launches per level:
+//   tile_sum      every 8192-addend tile of every big node: its plain fp64 sum (any order);
+//   tile_summary  the fp64 prefix of the tiles before it tells a tile, to ~1e-4, what the f32 accumulator
+//                 will be when the fold reaches it, i.e. its BINADE; the tile's composed parity function is
+//                 evaluated for that binade — all tiles of all nodes in parallel;
+//   resolve       one block per (node, axis) walks the tiles in order with the true accumulator: a tile whose
+//                 guess holds (same binade, accumulator stays inside it) costs O(1); the others — tile 0 and
+//                 the ~1 tile per power of two the sum crosses — are folded by the block with the windowed
+//                 scan, restarting after each binade change.  Nothing depends on the guess being right.
+constexpr int kFoldThreads = 256;
+constexpr int kFoldChunk = 32;
+constexpr int kFoldTile = kFoldThreads * kFoldChunk; // 8192
+constexpr int kFoldHead = 1024;       // addends at the start of a fold taken by a plain loop
+constexpr uint32_t kTileSlotShift = 12; // slot of a node's tile j = (start >> 12) + j: collision-free for len > 4096
+
+struct TileGuess { // 32 B
+  int32_t tot[2], lo[2], hi[2];
+  uint32_t key; // biased exponent | sign of the guessed accumulator; 0 = no guess
+  uint32_t pad;
+};
 
 __device__ __forceinline__ sf::Summary shfl_up_summary(const sf::Summary &s, int o) {
   sf::Summary t;
@@ -148,78 +165,117 @@ __device__ __forceinline__ sf::Summary shfl_up_summary(const sf::Summary &s, int
   return t;
 }
 
-// Exact sequential f32 sum of x[0..len) evaluated by the whole block (see seqfold_core.h).
-__device__ float block_seqfold(const float *__restrict__ x, uint32_t len) {
-  __shared__ float sx[kFoldWindow + kFoldWindow / 32];
-  __shared__ sf::Summary wsum[kFoldThreads / 32];
-  __shared__ float acc_s;
-  __shared__ uint32_t pos_s;
+struct FoldSmem {
+  float sx[kFoldTile + kFoldTile / 32]; // index i lives at i + (i >> 5): chunk-strided reads hit distinct banks
+  sf::Summary wsum[kFoldThreads / 32];
+  float acc;
+  uint32_t pos;
+};
+
+// Summaries of the window staged in sm.sx: thread t owns addends [t*cpt, (t+1)*cpt) below wlen.
+// Returns the thread's own summary; `pre` = composition of everything before it; sm.wsum[last] = whole window.
+__device__ __forceinline__ sf::Summary window_scan(FoldSmem &sm, const sf::Binade &b, uint32_t wlen, uint32_t cpt,
+                                                   sf::Summary &pre) {
   const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  if (tid == 0) { acc_s = 0.f; pos_s = 0; }
+  const uint32_t c0 = tid * cpt;
+  sf::Summary own = sf::identity();
+  bool bad = false;
+  for (uint32_t j = 0; j < cpt; ++j) {
+    const uint32_t i = c0 + j;
+    if (i < wlen) {
+      const sf::QElem q = sf::quantize(sm.sx[i + (i >> 5)], b);
+      bad = bad || q.c == 3;
+      sf::push_fast(own, q.n, q.c); // a bad addend (c == 3) poisons the chunk below
+    }
+  }
+  if (bad) sf::poison(own);
+  sf::Summary inc = own;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const sf::Summary t = shfl_up_summary(inc, o);
+    if (lane >= (unsigned)o) inc = sf::compose(t, inc);
+  }
+  __syncthreads(); // wsum free
+  if (lane == 31) sm.wsum[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    sf::Summary v = lane < kFoldThreads / 32 ? sm.wsum[lane] : sf::identity();
+#pragma unroll
+    for (int o = 1; o < kFoldThreads / 32; o <<= 1) {
+      const sf::Summary t = shfl_up_summary(v, o);
+      if (lane >= (unsigned)o) v = sf::compose(t, v);
+    }
+    if (lane < kFoldThreads / 32) sm.wsum[lane] = v; // inclusive over warps
+  }
+  __syncthreads();
+  pre = shfl_up_summary(inc, 1);
+  if (lane == 0) pre = sf::identity();
+  if (w > 0) pre = sf::compose(sm.wsum[w - 1], pre);
+  return own;
+}
+
+// acc folded over x[0..len), exactly as the sequential loop would, by the whole block.  `consumed` = addends the
+// fold saw before x[0]: early in a fold the sum doubles (changes binade) every few addends, so windows start small.
+__device__ float block_seqfold(FoldSmem &sm, const float *__restrict__ x, uint32_t len, float acc0, uint32_t consumed) {
+  const unsigned tid = threadIdx.x;
+  __syncthreads();
+  if (consumed == 0) {
+    // the first addends change the binade every few steps (the sum doubles): one thread folds them plainly
+    const uint32_t head = min(len, (uint32_t)kFoldHead);
+    for (uint32_t i = tid; i < head; i += kFoldThreads) sm.sx[i] = x[i];
+    __syncthreads();
+    if (tid == 0) {
+      float a = acc0;
+      uint32_t i = 0;
+      for (; i + 8 <= head; i += 8) {
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = sm.sx[i + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a = __fadd_rn(a, v[k]);
+      }
+      for (; i < head; ++i) a = __fadd_rn(a, sm.sx[i]);
+      sm.acc = a;
+      sm.pos = head;
+    }
+  } else if (tid == 0) { sm.acc = acc0; sm.pos = 0; }
   __syncthreads();
   for (;;) {
-    const float acc = acc_s;
-    const uint32_t pos = pos_s;
+    const float acc = sm.acc;
+    const uint32_t pos = sm.pos;
     if (pos >= len) return acc;
     sf::Binade b;
     if (!sf::binade_of(acc, b)) { // zero / subnormal / non-finite accumulator: one plain step
       __syncthreads();
-      if (tid == 0) { acc_s = __fadd_rn(acc, x[pos]); pos_s = pos + 1; }
+      if (tid == 0) { sm.acc = __fadd_rn(acc, x[pos]); sm.pos = pos + 1; }
       __syncthreads();
       continue;
     }
-    const uint32_t wlen = min((uint32_t)kFoldWindow, len - pos);
-    for (uint32_t i = tid; i < wlen; i += kFoldThreads) sx[i + (i >> 5)] = x[pos + i];
+    const uint32_t grow = max((uint32_t)kFoldThreads, 2u * (consumed + pos));
+    const uint32_t wlen = min(min((uint32_t)kFoldTile, len - pos), grow);
+    const uint32_t cpt = (wlen + kFoldThreads - 1) / kFoldThreads;
+    for (uint32_t i = tid; i < wlen; i += kFoldThreads) sm.sx[i + (i >> 5)] = x[pos + i];
     __syncthreads();
-    const uint32_t c0 = tid * kFoldChunk;
-    sf::Summary own = sf::identity();
-#pragma unroll
-    for (int j = 0; j < kFoldChunk; ++j) {
-      const uint32_t i = c0 + j;
-      if (i < wlen) sf::push(own, sf::quantize(sx[i + (i >> 5)], b));
-    }
-    // inclusive scan of the chunk functions in sequence order
-    sf::Summary inc = own;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const sf::Summary t = shfl_up_summary(inc, o);
-      if (lane >= (unsigned)o) inc = sf::compose(t, inc);
-    }
-    if (lane == 31) wsum[w] = inc;
-    __syncthreads();
-    if (w == 0) {
-      sf::Summary v = wsum[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const sf::Summary t = shfl_up_summary(v, o);
-        if (lane >= (unsigned)o) v = sf::compose(t, v);
-      }
-      wsum[lane] = v; // inclusive over warps
-    }
-    __syncthreads();
-    sf::Summary pre = shfl_up_summary(inc, 1); // exclusive within the warp
-    if (lane == 0) pre = sf::identity();
-    if (w > 0) pre = sf::compose(wsum[w - 1], pre);
+    sf::Summary pre;
+    const sf::Summary own = window_scan(sm, b, wlen, cpt, pre);
     const int p0 = b.A & 1;
-    const bool prefix_ok = sf::valid_from(pre, b.A);
     const int32_t Ain = b.A + pre.tot[p0];
-    const bool bad = prefix_ok && !sf::valid_from(own, Ain);
+    const bool bad = sf::valid_from(pre, b.A) && !sf::valid_from(own, Ain);
     const int any_bad = __syncthreads_or(bad);
     if (!any_bad) {
-      if (tid == kFoldThreads - 1) {
-        const sf::Summary all = wsum[kFoldThreads / 32 - 1];
-        acc_s = sf::binade_value(b, b.A + all.tot[p0]);
-        pos_s = pos + wlen;
+      if (tid == 0) {
+        sm.acc = sf::binade_value(b, b.A + sm.wsum[kFoldThreads / 32 - 1].tot[p0]);
+        sm.pos = pos + wlen;
       }
     } else if (bad) { // the first chunk in which the accumulator leaves the binade: walk it
       int32_t Ar = Ain;
-      for (int j = 0; j < kFoldChunk; ++j) {
-        const uint32_t i = c0 + j;
-        const float xv = sx[i + (i >> 5)];
+      for (uint32_t j = 0; j < cpt; ++j) {
+        const uint32_t i = tid * cpt + j;
+        const float xv = sm.sx[i + (i >> 5)];
         const sf::QElem q = sf::quantize(xv, b);
         if (!sf::step_valid(q, Ar)) {
-          acc_s = __fadd_rn(sf::binade_value(b, Ar), xv);
-          pos_s = pos + i + 1;
+          sm.acc = __fadd_rn(sf::binade_value(b, Ar), xv);
+          sm.pos = pos + i + 1;
           break;
         }
         Ar = sf::step_apply(q, Ar);
@@ -229,20 +285,119 @@ __device__ float block_seqfold(const float *__restrict__ x, uint32_t len) {
   }
 }
 
-__global__ void __launch_bounds__(kFoldThreads) bvh_fold_big_kernel(BvhWork W, int level) {
+struct TileArrays {
+  double *sum[2];     // [axis][slot]
+  TileGuess *guess[2];
+};
+
+__global__ void __launch_bounds__(kFoldThreads) bvh_tile_sum_kernel(BvhWork W, TileArrays TA, int level) {
+  __shared__ double red[kFoldThreads / 32];
   const uint32_t cnt = W.meta->cnt_big[level];
   const uint32_t *list = W.list_big[level & 1];
-  const bool ydim = blockIdx.y != 0;
+  const int dim = blockIdx.z;
+  const float *src = dim ? W.wy : W.wx;
   for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
     const uint32_t ni = list[a];
     const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
-    const float sum = block_seqfold((ydim ? W.wy : W.wx) + s, len);
+    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
+    for (uint32_t j = blockIdx.y; j + 1 < ntiles; j += gridDim.y) { // the last tile's sum is never needed
+      const float *x = src + s + (size_t)j * kFoldTile;
+      double v = 0.0;
+#pragma unroll 8
+      for (uint32_t i = threadIdx.x; i < (uint32_t)kFoldTile; i += kFoldThreads) v += (double)x[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      __syncthreads();
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < kFoldThreads / 32; ++k) t += red[k];
+        TA.sum[dim][slot0 + j] = t;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kFoldThreads) bvh_tile_summary_kernel(BvhWork W, TileArrays TA, int level) {
+  __shared__ FoldSmem sm;
+  __shared__ double red[kFoldThreads / 32];
+  const uint32_t cnt = W.meta->cnt_big[level];
+  const uint32_t *list = W.list_big[level & 1];
+  const int dim = blockIdx.z;
+  const float *src = dim ? W.wy : W.wx;
+  for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
+    const uint32_t ni = list[a];
+    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
+    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
+    for (uint32_t j = 1 + blockIdx.y; j < ntiles; j += gridDim.y) {
+      // fp64 prefix of the tiles before j
+      double v = 0.0;
+      for (uint32_t k = threadIdx.x; k < j; k += kFoldThreads) v += TA.sum[dim][slot0 + k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      __syncthreads();
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+      __syncthreads();
+      double P = 0.0;
+      for (int k = 0; k < kFoldThreads / 32; ++k) P += red[k];
+      sf::Binade b;
+      TileGuess g{};
+      if (sf::binade_of(__double2float_rn(P), b)) { // uniform across the block
+        const uint32_t tlen = min((uint32_t)kFoldTile, len - j * kFoldTile);
+        const float *x = src + s + (size_t)j * kFoldTile;
+        for (uint32_t i = threadIdx.x; i < tlen; i += kFoldThreads) sm.sx[i + (i >> 5)] = x[i];
+        __syncthreads();
+        sf::Summary pre;
+        window_scan(sm, b, tlen, kFoldChunk, pre);
+        const sf::Summary all = sm.wsum[kFoldThreads / 32 - 1];
+        g.tot[0] = all.tot[0]; g.tot[1] = all.tot[1];
+        g.lo[0] = all.lo[0]; g.lo[1] = all.lo[1];
+        g.hi[0] = all.hi[0]; g.hi[1] = all.hi[1];
+        g.key = b.E | b.sign;
+      }
+      if (threadIdx.x == 0) TA.guess[dim][slot0 + j] = g;
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kFoldThreads) bvh_fold_resolve_kernel(BvhWork W, TileArrays TA, int level) {
+  __shared__ FoldSmem sm;
+  const uint32_t cnt = W.meta->cnt_big[level];
+  const uint32_t *list = W.list_big[level & 1];
+  const int dim = blockIdx.y;
+  const float *src = dim ? W.wy : W.wx;
+  for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
+    const uint32_t ni = list[a];
+    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
+    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
+    float acc = 0.f;
+    for (uint32_t j = 0; j < ntiles; ++j) {
+      bool fast = false;
+      sf::Binade b;
+      if (j > 0 && sf::binade_of(acc, b)) {
+        const TileGuess g = TA.guess[dim][slot0 + j];
+        if (g.key == (b.E | b.sign)) {
+          sf::Summary S;
+          S.tot[0] = g.tot[0]; S.tot[1] = g.tot[1];
+          S.lo[0] = g.lo[0]; S.lo[1] = g.lo[1];
+          S.hi[0] = g.hi[0]; S.hi[1] = g.hi[1];
+          if (sf::valid_from(S, b.A)) {
+            acc = sf::binade_value(b, b.A + S.tot[b.A & 1]);
+            fast = true;
+          }
+        }
+      }
+      if (!fast)
+        acc = block_seqfold(sm, src + s + (size_t)j * kFoldTile, min((uint32_t)kFoldTile, len - j * kFoldTile), acc,
+                            j * kFoldTile);
+    }
     if (threadIdx.x == 0) {
-      const float mean = __fdiv_rn(sum, __uint2float_rn(len));
-      if (ydim) { W.nodes[ni].meany = mean; W.nodes[ni].cy = 0; }
+      const float mean = __fdiv_rn(acc, __uint2float_rn(len)); // `points.len() as f32`, bvh_tree.rs:67
+      if (dim) { W.nodes[ni].meany = mean; W.nodes[ni].cy = 0; }
       else { W.nodes[ni].meanx = mean; W.nodes[ni].cx = 0; }
     }
-    __syncthreads();
   }
 }
 

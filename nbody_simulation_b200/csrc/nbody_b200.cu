@@ -87,6 +87,7 @@ struct nb_ctx {
   bool quad = true;
   bool bvh_ref = false;   // NB_TREE_BVH_REF: level-synchronous BVHTree::from (bvh_ref.cuh)
   BvhWork bw{};
+  TileArrays tiles{};
   BvhMeta *h_bmeta = nullptr; // pinned mirror of bw.meta
   uint32_t bvh_levels = 0;    // levels of the last build
 
@@ -183,7 +184,14 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
     if (c->h_bmeta->n_nodes + 2 * (nbig + nsmall) > W.node_cap)
       return fail(c, NB_ERR_OVERFLOW, "BVH node pool too small");
     if (nsmall) bvh_fold_small_kernel<<<std::min(cdiv(nsmall, 8u), (uint32_t)kSMs * 8u), 256, 0, st>>>(W, level);
-    if (nbig) bvh_fold_big_kernel<<<dim3(std::min(nbig, (uint32_t)kSMs * 2u), 2), kFoldThreads, 0, st>>>(W, level);
+    if (nbig) {
+      // tiles of one node are spread over blockIdx.y; with many nodes one block per node suffices
+      const uint32_t gx = std::min(nbig, (uint32_t)kSMs * 4u);
+      const uint32_t gy = std::max(1u, std::min(64u, cdiv(cdiv(n, (uint32_t)kFoldTile), nbig)));
+      bvh_tile_sum_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+      bvh_tile_summary_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+      bvh_fold_resolve_kernel<<<dim3(gx, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+    }
     bvh_count_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
     bvh_decide_kernel<<<cdiv(nbig + nsmall, 256), 256, 0, st>>>(W, level, (uint32_t)c->leaf_cap);
     bvh_flag_reduce_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
@@ -191,7 +199,7 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
     bvh_flag_apply_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
     bvh_publish_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
     bvh_swap_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
-    g_launches += 7 + (nsmall ? 1 : 0) + (nbig ? 1 : 0);
+    g_launches += 7 + (nsmall ? 1 : 0) + (nbig ? 3 : 0);
   }
   c->bvh_levels = (uint32_t)level;
   bvh_sizes_kernel<<<kSMs * 8, 256, 0, st>>>(W);
@@ -438,7 +446,10 @@ void nb_destroy(nb_ctx *c) {
   if (c->h_meta) cudaFreeHost(c->h_meta);
   if (c->h_bmeta) cudaFreeHost(c->h_bmeta);
   cudaFree(c->bw.nodes); cudaFree(c->bw.meta);
-  for (int i = 0; i < 2; ++i) { cudaFree(c->bw.list_big[i]); cudaFree(c->bw.list_small[i]); }
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(c->bw.list_big[i]); cudaFree(c->bw.list_small[i]);
+    cudaFree(c->tiles.sum[i]); cudaFree(c->tiles.guess[i]);
+  }
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -532,6 +543,11 @@ nb_ctx *nb_create(const nb_config *cfg) {
     }
     NB_TRY(dmalloc(&W.meta, 1));
     NB_TRY(cudaMallocHost((void **)&c->h_bmeta, sizeof(BvhMeta)));
+    const size_t slots = (na >> kTileSlotShift) + 8;
+    for (int i = 0; i < 2; ++i) {
+      NB_TRY(dmalloc(&c->tiles.sum[i], slots));
+      NB_TRY(dmalloc(&c->tiles.guess[i], slots));
+    }
   }
   Meta m0{};
   m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;

@@ -151,6 +151,21 @@ NB_HD void push(Summary &s, const QElem &q) {
     s.tot[p] = clampi(f + (q.c == 2 ? 1 : (q.c == 1 ? odd : 0)));
   }
 }
+// push() for a quantised addend known not to be bad and a chunk short enough (<= 64 addends of |n| <= 2^24)
+// that the int32 fields cannot overflow: (c >> 1) is "round up", (c & (f ^ p) & 1) is "tie and floor odd".
+NB_HD void push_fast(Summary &s, int32_t n, int32_t c) {
+  NB_UNROLL
+  for (int p = 0; p < 2; ++p) {
+    const int32_t f = s.tot[p] + n;
+    s.lo[p] = f < s.lo[p] ? f : s.lo[p];
+    s.hi[p] = f > s.hi[p] ? f : s.hi[p];
+    s.tot[p] = f + ((c >> 1) | (c & (f ^ p) & 1));
+  }
+}
+NB_HD void poison(Summary &s) { // a chunk holding an addend the binade cannot take
+  s.lo[0] = s.lo[1] = -kBig;
+  s.hi[0] = s.hi[1] = kBig;
+}
 // h = g after f
 NB_HD Summary compose(const Summary &f, const Summary &g) {
   Summary h;
@@ -161,7 +176,7 @@ NB_HD Summary compose(const Summary &f, const Summary &g) {
     const int32_t l2 = clampi((int64_t)f.tot[p] + g.lo[q]), h2 = clampi((int64_t)f.tot[p] + g.hi[q]);
     h.lo[p] = f.lo[p] < l2 ? f.lo[p] : l2;
     h.hi[p] = f.hi[p] > h2 ? f.hi[p] : h2;
-    if (g.lo[q] >= kBig) { h.lo[p] = f.lo[p]; h.hi[p] = f.hi[p]; } // g empty
+    if (g.hi[q] < g.lo[q]) { h.lo[p] = f.lo[p]; h.hi[p] = f.hi[p]; } // g empty
   }
   return h;
 }
@@ -169,7 +184,7 @@ NB_HD Summary compose(const Summary &f, const Summary &g) {
 // floor in [2^23, 2^24 - 2], so the rounded value is < 2^24 too).
 NB_HD bool valid_from(const Summary &s, int32_t A) {
   const int p = A & 1;
-  if (s.lo[p] >= kBig) return true; // empty
+  if (s.hi[p] < s.lo[p]) return true; // empty
   return (int64_t)A + s.lo[p] >= kLoA && (int64_t)A + s.hi[p] <= kHiA - 2;
 }
 NB_HD bool step_valid(const QElem &q, int32_t A) {

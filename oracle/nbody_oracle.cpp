@@ -1088,16 +1088,18 @@ int orc_world_update(void *h, int kind, float delta, float theta, float x0, floa
 // the product; it sizes the GPU traversal (SIMD efficiency of warp-cooperative walks).
 // out[0]=groups, [1]=internal node visits, [2]=leaf visits, [3]=sum of unmasked bodies at internal
 // visits (= opening tests), [4]=accepted (node interactions), [5]=leaf-body pair interactions,
-// [6]=sum over leaf visits of leaf body count (uniform loop trips), [7]=sum of unmasked bodies at leaf visits
+// [6]=sum over leaf visits of leaf body count (uniform loop trips), [7]=sum of unmasked bodies at leaf visits,
+// [8]/[9]/[10]=internal visits where every unmasked body accepts / none accepts / they disagree,
+// [11]=internal visits with all G bodies unmasked
 int orc_group_walk_stats(void *h, float theta, int G, double *out) {
   OrcTree *T = (OrcTree *)h;
   const FlatTree &t = T->flat;
   const uint32_t nn = (uint32_t)t.depth.size();
   const size_t n = t.n;
-  double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  double acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 #pragma omp parallel
   {
-    double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    double a[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<uint32_t> resume(G);
 #pragma omp for schedule(dynamic, 64)
     for (long long g0 = 0; g0 < (long long)n; g0 += G) {
@@ -1114,23 +1116,27 @@ int orc_group_walk_stats(void *h, float theta, int G, double *out) {
         } else {
           a[1] += 1;
           bool any_open = false;
+          int n_act = 0, n_acc = 0;
           V2 cog{t.cogx[cur], t.cogy[cur]};
           for (int k = 0; k < gs; ++k) {
             if (cur < resume[k]) continue;
             a[3] += 1;
+            n_act++;
             V2 p{t.sx[g0 + k], t.sy[g0 + k]};
             bool contains = p.y > t.y0[cur] && p.x > t.x0[cur] && p.x < t.x1[cur] && p.y < t.y1[cur];
-            if (!contains && t.s2[cur] < dist2(p, cog) * theta * theta) { a[4] += 1; resume[k] = t.skip[cur]; }
+            if (!contains && t.s2[cur] < dist2(p, cog) * theta * theta) { a[4] += 1; n_acc++; resume[k] = t.skip[cur]; }
             else any_open = true;
           }
+          a[n_acc == n_act ? 8 : (n_acc == 0 ? 9 : 10)] += 1;
+          if (n_act == gs) a[11] += 1;
           cur = any_open ? cur + 1 : t.skip[cur];
         }
       }
     }
 #pragma omp critical
-    for (int k = 0; k < 8; ++k) acc[k] += a[k];
+    for (int k = 0; k < 12; ++k) acc[k] += a[k];
   }
-  for (int k = 0; k < 8; ++k) out[k] = acc[k];
+  for (int k = 0; k < 12; ++k) out[k] = acc[k];
   return 0;
 }
 

@@ -27,13 +27,13 @@ def scene():
 def build():
     p = scene()
     out = {"particles": p.view(np.uint8), "theta": np.float32(THETA), "dt": np.float32(DT), "steps": np.int32(STEPS)}
-    for name, kind in (("quad", ob.KIND_PIPE_QUAD), ("lbvh", ob.KIND_PIPE_LBVH)):
+    for name, kind in (("quad", ob.KIND_PIPE_QUAD), ("lbvh", ob.KIND_PIPE_LBVH), ("bvhref", ob.KIND_LITERAL_BVH)):
         T = ob.Tree(kind, p["x"], p["y"], p["weight"])
         t = T.export()
         for k, v in t.items():
             if k != "info":
                 out[f"{name}_{k}"] = v
-        ax, ay, ni, nt, _ = T.accel(THETA)
+        ax, ay, ni, nt, _ = T.accel(THETA, literal=(kind == ob.KIND_LITERAL_BVH))  # bvhref: recursive main.rs:349-386
         out[f"{name}_ax"], out[f"{name}_ay"] = ax, ay
         out[f"{name}_interactions"], out[f"{name}_tests"] = np.uint64(ni), np.uint64(nt)
         w = ob.OracleWorld(p)

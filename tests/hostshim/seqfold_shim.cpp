@@ -16,10 +16,16 @@ static float fold_scan(const float *x, size_t n, float acc, int chunk, int threa
     const size_t W = (size_t)chunk * threads, wlen = n - pos < W ? n - pos : W;
     for (int t = 0; t < threads; ++t) {
       own[t] = identity();
-      for (int j = 0; j < chunk; ++j) {
+      bool bad = false;
+      for (int j = 0; j < chunk; ++j) { // as window_scan() does on the device (chunk <= 32)
         size_t i = (size_t)t * chunk + j;
-        if (i < wlen) push(own[t], quantize(x[pos + i], b));
+        if (i < wlen) {
+          QElem q = quantize(x[pos + i], b);
+          bad = bad || q.c == 3;
+          push_fast(own[t], q.n, q.c);
+        }
       }
+      if (bad) poison(own[t]);
       inc[t] = own[t];
     }
     for (int o = 1; o < threads; o <<= 1) {

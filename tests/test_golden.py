@@ -19,13 +19,14 @@ def bits(a):
     return np.ascontiguousarray(a).view(np.uint8)
 
 
-@pytest.mark.parametrize("name,kind", [("quad", ob.KIND_PIPE_QUAD), ("lbvh", ob.KIND_PIPE_LBVH)])
+@pytest.mark.parametrize("name,kind", [("quad", ob.KIND_PIPE_QUAD), ("lbvh", ob.KIND_PIPE_LBVH),
+                                       ("bvhref", ob.KIND_LITERAL_BVH)])
 def test_oracle_reproduces_golden(name, kind):
     T = ob.Tree(kind, P["x"], P["y"], P["weight"])
     t = T.export()
     for k in TREE_KEYS:
         assert np.array_equal(bits(t[k]), bits(G[f"{name}_{k}"])), k
-    ax, ay, ni, nt, _ = T.accel(float(G["theta"]))
+    ax, ay, ni, nt, _ = T.accel(float(G["theta"]), literal=(kind == ob.KIND_LITERAL_BVH))
     assert ni == int(G[f"{name}_interactions"]) and nt == int(G[f"{name}_tests"])
     assert np.array_equal(bits(ax), bits(G[f"{name}_ax"])) and np.array_equal(bits(ay), bits(G[f"{name}_ay"]))
     w = ob.OracleWorld(P)
@@ -42,14 +43,15 @@ def test_golden_literal_quadtree_matches_too():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,tree", [("quad", nb.NB_TREE_QUAD), ("lbvh", nb.NB_TREE_LBVH)])
+@pytest.mark.parametrize("name,tree", [("quad", nb.NB_TREE_QUAD), ("lbvh", nb.NB_TREE_LBVH),
+                                       ("bvhref", nb.NB_TREE_BVH_REF)])
 def test_cuda_reproduces_golden(name, tree):
     w = nb.World(len(P), theta=float(G["theta"]), dt=float(G["dt"]), tree=tree, force_mode=nb.NB_FORCE_EXACT)
     w.set_particles(P)
     c = nb.Counting()
     ax, ay = w.accel(c)
     t = w.tree()
-    for k in TREE_KEYS:
+    for k in TREE_KEYS[1:] if name == "bvhref" else TREE_KEYS:  # the reference BVH has no Morton keys
         assert np.array_equal(bits(t[k]), bits(G[f"{name}_{k}"])), k
     assert c.interactions == int(G[f"{name}_interactions"]) and c.node_tests == int(G[f"{name}_tests"])
     assert np.array_equal(bits(ax), bits(G[f"{name}_ax"])) and np.array_equal(bits(ay), bits(G[f"{name}_ay"]))
