@@ -23,11 +23,13 @@
 
 namespace nb {
 
-constexpr uint32_t kBvhSmall = 4096;    // fold by one warp up to this many bodies
+constexpr uint32_t kBvhSmall = 4096;    // a node of at most this many bodies is finished, subtree and all, by one
+                                        // block in shared memory (bvh_subtree_kernel)
 constexpr int kBvhMaxLevels = 96;       // the reference recurses without bound (stack overflow on
                                         // coincident bodies); here the remaining nodes become leaves
 constexpr uint32_t kBNodeLeaf = 0x40000000u;
 constexpr uint32_t kBNodeAxisX = 0x80000000u;
+constexpr uint32_t kBNodeSub = 0x20000000u; // root of a small subtree: not split by the level-synchronous kernels
 
 struct BNode { // 48 B, breadth-first pool
   uint32_t start, len;
@@ -44,15 +46,16 @@ struct BNode { // 48 B, breadth-first pool
 struct BvhMeta {
   uint32_t n_nodes;
   uint32_t overflow;                 // leaves forced at the level cap
-  uint32_t cnt_big[kBvhMaxLevels + 2];   // active nodes per level, by fold class
-  uint32_t cnt_small[kBvhMaxLevels + 2];
+  uint32_t cnt_big[kBvhMaxLevels + 2];   // big nodes to split, per level
+  uint32_t cnt_sub;                      // small-subtree roots (any level)
   uint32_t levels;                   // levels actually built (host bookkeeping)
 };
 
 struct BvhWork {
   BNode *nodes;
   uint32_t node_cap;
-  uint32_t *list_big[2], *list_small[2]; // ping-pong by level parity
+  uint32_t *list_big[2]; // ping-pong by level parity
+  uint32_t *list_sub;    // roots of small subtrees
   float *wx, *wy;     // positions in the current (partially partitioned) order
   uint32_t *order;    // position -> storage slot of the body
   uint32_t *seg;      // position -> pool index of the node that currently owns the body
@@ -77,12 +80,13 @@ __global__ void __launch_bounds__(256) bvh_init_kernel(BvhWork W, Meta *meta, co
     r.start = 0;
     r.len = n;
     r.parent = 0xffffffffu;
-    r.flags = 0; // level 0; always a Root (bvh_tree.rs:90), even with <= 64 bodies
+    r.flags = n > kBvhSmall ? 0u : kBNodeSub; // level 0; always a Root (bvh_tree.rs:90), even with <= 64 bodies
     W.nodes[0] = r;
     BvhMeta *m = W.meta;
     m->n_nodes = 1;
     m->overflow = 0;
-    for (int l = 0; l < kBvhMaxLevels + 2; ++l) m->cnt_big[l] = m->cnt_small[l] = 0;
+    for (int l = 0; l < kBvhMaxLevels + 2; ++l) m->cnt_big[l] = 0;
+    m->cnt_sub = 0;
     meta->n = n; // per-step metadata (the Morton pipeline initialises it in its sort)
     meta->n_in = n;
     meta->n_nodes = 0;
@@ -91,44 +95,7 @@ __global__ void __launch_bounds__(256) bvh_init_kernel(BvhWork W, Meta *meta, co
     meta->overflow_leaves = 0;
     meta->cog_outside = 0;
     if (n > kBvhSmall) { m->cnt_big[0] = 1; W.list_big[0][0] = 0; }
-    else { m->cnt_small[0] = 1; W.list_small[0][0] = 0; }
-  }
-}
-
-// ---- fold, small nodes: one warp per node, both axes, literally sequential ---------------------------
-__global__ void __launch_bounds__(256) bvh_fold_small_kernel(BvhWork W, int level) {
-  const uint32_t cnt = W.meta->cnt_small[level];
-  const uint32_t *list = W.list_small[level & 1];
-  const unsigned lane = threadIdx.x & 31;
-  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t a = warp; a < cnt; a += nwarps) {
-    const uint32_t ni = list[a];
-    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
-    float ax = 0.f, ay = 0.f;
-    for (uint32_t base = 0; base < len; base += 32) {
-      const uint32_t c = min(32u, len - base);
-      const float vx = lane < c ? W.wx[s + base + lane] : 0.f;
-      const float vy = lane < c ? W.wy[s + base + lane] : 0.f;
-      if (c == 32) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
-          ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
-        }
-      } else {
-        for (uint32_t j = 0; j < c; ++j) {
-          ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
-          ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
-        }
-      }
-    }
-    if (lane == 0) {
-      const float lf = __uint2float_rn(len); // `points.len() as f32`, bvh_tree.rs:67
-      W.nodes[ni].meanx = __fdiv_rn(ax, lf);
-      W.nodes[ni].meany = __fdiv_rn(ay, lf);
-      W.nodes[ni].cx = 0;
-      W.nodes[ni].cy = 0;
-    }
+    else { m->cnt_sub = 1; W.list_sub[0] = 0; }
   }
 }
 
@@ -438,10 +405,10 @@ __global__ void __launch_bounds__(256) bvh_count_kernel(BvhWork W, uint32_t n, i
 // ---- decide: axis, split point, children, next level's lists (bvh_tree.rs:69-88) -------------------------
 __global__ void __launch_bounds__(256) bvh_decide_kernel(BvhWork W, int level, uint32_t target) {
   BvhMeta *m = W.meta;
-  const uint32_t nb = m->cnt_big[level], ns = m->cnt_small[level];
+  const uint32_t nb = m->cnt_big[level];
   const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= nb + ns) return;
-  const uint32_t ni = a < nb ? W.list_big[level & 1][a] : W.list_small[level & 1][a - nb];
+  if (a >= nb) return;
+  const uint32_t ni = W.list_big[level & 1][a];
   BNode &nd = W.nodes[ni];
   const uint32_t len = nd.len, half = len / 2;
   const uint32_t hori = half > nd.cx ? half - nd.cx : nd.cx - half; // abs_diff, bvh_tree.rs:71
@@ -462,7 +429,10 @@ __global__ void __launch_bounds__(256) bvh_decide_kernel(BvhWork W, int level, u
     if (internal && level + 1 < kBvhMaxLevels) {
       ch.flags = (uint32_t)(level + 1);
       if (ch.len > kBvhSmall) W.list_big[(level + 1) & 1][atomicAdd(&m->cnt_big[level + 1], 1u)] = c0 + k;
-      else W.list_small[(level + 1) & 1][atomicAdd(&m->cnt_small[level + 1], 1u)] = c0 + k;
+      else {
+        ch.flags |= kBNodeSub;
+        W.list_sub[atomicAdd(&m->cnt_sub, 1u)] = c0 + k;
+      }
     } else {
       ch.flags = (uint32_t)(level + 1) | kBNodeLeaf;
       ch.size = 1;
@@ -541,6 +511,204 @@ __global__ void __launch_bounds__(256) bvh_swap_kernel(BvhWork W, uint32_t n, in
   const uint32_t oi = W.order[i];
   W.wx[i] = W.wx[j]; W.wy[i] = W.wy[j]; W.order[i] = W.order[j];
   W.wx[j] = xi; W.wy[j] = yi; W.order[j] = oi;
+}
+
+// ---- small subtrees: one block finishes a node of <= kBvhSmall bodies, all levels below it, in smem -----------
+// Same steps as the level-synchronous kernels above (fold -> count -> decide -> flag scan -> publish -> swap),
+// over the bodies of one subtree held in shared memory; nodes are appended to the global pool.
+constexpr int kSubThreads = 256;
+constexpr int kSubItems = kBvhSmall / kSubThreads; // 16
+constexpr uint16_t kSubSettled = 0xffffu;
+
+struct SubAct { // an internal node of the current local level
+  uint32_t gidx;        // index in the global pool
+  uint32_t start, len;  // relative to the subtree's first body
+  float meanx, meany;
+  uint32_t cx, cy, T, xaxis;
+  uint32_t slot[2];     // children: index in the next level's list, or kSubSettled
+};
+struct SubSmem {
+  float x[kBvhSmall], y[kBvhSmall];
+  uint32_t ord[kBvhSmall];
+  uint16_t seg[kBvhSmall]; // body -> index in the current level's list, kSubSettled once its leaf exists
+  uint16_t F[kBvhSmall];   // exclusive prefix of predicate-false flags
+  uint16_t lt[kBvhSmall];  // misplaced predicate-true bodies by rank from the right
+  SubAct act[2][64];       // > 64 bodies per internal node: at most 63 per level
+  uint32_t nact[2];
+};
+
+__global__ void __launch_bounds__(kSubThreads) bvh_subtree_kernel(BvhWork W, uint32_t target) {
+  extern __shared__ __align__(16) unsigned char sub_raw[];
+  SubSmem &sm = *reinterpret_cast<SubSmem *>(sub_raw);
+  BvhMeta *m = W.meta;
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t nsub = m->cnt_sub;
+  for (uint32_t r = blockIdx.x; r < nsub; r += gridDim.x) {
+    const uint32_t groot = W.list_sub[r];
+    const uint32_t s0 = W.nodes[groot].start, L = W.nodes[groot].len;
+    int level = (int)(W.nodes[groot].flags & 0xffffu);
+    __syncthreads();
+    for (uint32_t i = tid; i < L; i += kSubThreads) {
+      sm.x[i] = W.wx[s0 + i];
+      sm.y[i] = W.wy[s0 + i];
+      sm.ord[i] = W.order[s0 + i];
+      sm.seg[i] = 0;
+    }
+    if (tid == 0) {
+      sm.act[0][0].gidx = groot;
+      sm.act[0][0].start = 0;
+      sm.act[0][0].len = L;
+      sm.nact[0] = 1;
+      sm.nact[1] = 0;
+    }
+    __syncthreads();
+    int cur = 0;
+    for (;; ++level, cur ^= 1) {
+      const uint32_t na = sm.nact[cur];
+      if (na == 0) break;
+      // fold (bvh_tree.rs:58-61,67): one warp per node, literally sequential
+      for (uint32_t a = warp; a < na; a += kSubThreads / 32) {
+        SubAct &A = sm.act[cur][a];
+        const uint32_t s = A.start, len = A.len;
+        float ax = 0.f, ay = 0.f;
+        for (uint32_t base = 0; base < len; base += 32) {
+          const uint32_t c = min(32u, len - base);
+          const float vx = lane < c ? sm.x[s + base + lane] : 0.f;
+          const float vy = lane < c ? sm.y[s + base + lane] : 0.f;
+          if (c == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
+              ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
+            }
+          } else {
+            for (uint32_t j = 0; j < c; ++j) {
+              ax = __fadd_rn(ax, __shfl_sync(0xffffffffu, vx, j));
+              ay = __fadd_rn(ay, __shfl_sync(0xffffffffu, vy, j));
+            }
+          }
+        }
+        if (lane == 0) {
+          const float lf = __uint2float_rn(len);
+          A.meanx = __fdiv_rn(ax, lf);
+          A.meany = __fdiv_rn(ay, lf);
+          A.cx = 0;
+          A.cy = 0;
+        }
+      }
+      if (tid == 0) sm.nact[cur ^ 1] = 0;
+      __syncthreads();
+      // count (bvh_tree.rs:70-72)
+      for (uint32_t i = tid; i < L; i += kSubThreads) {
+        const uint32_t a = sm.seg[i];
+        if (a == kSubSettled) continue;
+        SubAct &A = sm.act[cur][a];
+        if (sm.x[i] > A.meanx) atomicAdd(&A.cx, 1u);
+        if (sm.y[i] > A.meany) atomicAdd(&A.cy, 1u);
+      }
+      __syncthreads();
+      // decide (bvh_tree.rs:69-88)
+      if (tid < na) {
+        SubAct &A = sm.act[cur][tid];
+        const uint32_t len = A.len, half = len / 2;
+        const uint32_t hori = half > A.cx ? half - A.cx : A.cx - half;
+        const uint32_t vert = half > A.cy ? half - A.cy : A.cy - half;
+        const bool xaxis = vert > hori;
+        const uint32_t T = xaxis ? A.cx : A.cy;
+        A.T = T;
+        A.xaxis = xaxis ? 1u : 0u;
+        const uint32_t c0 = atomicAdd(&m->n_nodes, 2u);
+        const bool room = c0 + 2 <= W.node_cap; // else: reported by the emit kernel (n_nodes > capacity)
+        BNode &nd = W.nodes[A.gidx];
+        nd.T = T;
+        nd.flags = (uint32_t)level | (xaxis ? kBNodeAxisX : 0u);
+        nd.child0 = room ? c0 : 0u;
+        for (int k = 0; k < 2; ++k) {
+          BNode ch{};
+          ch.start = s0 + A.start + (k ? T : 0u);
+          ch.len = k ? len - T : T;
+          ch.parent = A.gidx;
+          const bool internal = ch.len > target;
+          uint32_t slot = kSubSettled;
+          if (internal && level + 1 < kBvhMaxLevels && room) {
+            ch.flags = (uint32_t)(level + 1);
+            slot = atomicAdd(&sm.nact[cur ^ 1], 1u);
+            SubAct &B = sm.act[cur ^ 1][slot];
+            B.gidx = c0 + k;
+            B.start = A.start + (k ? T : 0u);
+            B.len = ch.len;
+          } else {
+            ch.flags = (uint32_t)(level + 1) | kBNodeLeaf;
+            ch.size = 1;
+            if (internal && room) atomicAdd(&m->overflow, 1u);
+          }
+          A.slot[k] = slot;
+          if (room) W.nodes[c0 + k] = ch;
+        }
+      }
+      __syncthreads();
+      // exclusive scan of the predicate-false flags over the whole subtree
+      {
+        const uint32_t i0 = tid * kSubItems;
+        uint32_t v[kSubItems], ssum = 0;
+#pragma unroll
+        for (int k = 0; k < kSubItems; ++k) {
+          const uint32_t i = i0 + k;
+          uint32_t f = 0;
+          if (i < L) {
+            const uint32_t a = sm.seg[i];
+            if (a != kSubSettled) {
+              const SubAct &A = sm.act[cur][a];
+              const bool pred = A.xaxis ? (sm.x[i] > A.meanx) : (sm.y[i] > A.meany);
+              f = pred ? 0u : 1u;
+            }
+          }
+          v[k] = f;
+          ssum += f;
+        }
+        uint32_t tot;
+        uint32_t ex = block_exclusive_scan<kSubThreads>(ssum, tot);
+#pragma unroll
+        for (int k = 0; k < kSubItems; ++k) {
+          if (i0 + k < L) sm.F[i0 + k] = (uint16_t)ex;
+          ex += v[k];
+        }
+      }
+      __syncthreads();
+      // partition (bvh_tree.rs:74-76): publish the misplaced trues, then swap
+      for (uint32_t i = tid; i < L; i += kSubThreads) {
+        const uint32_t a = sm.seg[i];
+        if (a == kSubSettled) continue;
+        const SubAct &A = sm.act[cur][a];
+        if (i < A.start + A.T) continue;
+        const bool pred = A.xaxis ? (sm.x[i] > A.meanx) : (sm.y[i] > A.meany);
+        if (!pred) continue;
+        const uint32_t fb = (uint32_t)sm.F[i] - (uint32_t)sm.F[A.start];
+        const uint32_t tb = (i - A.start) - fb;
+        sm.lt[A.start + (A.T - tb - 1u)] = (uint16_t)i;
+      }
+      __syncthreads();
+      for (uint32_t i = tid; i < L; i += kSubThreads) {
+        const uint32_t a = sm.seg[i];
+        if (a == kSubSettled) continue;
+        const SubAct &A = sm.act[cur][a];
+        const bool left = i < A.start + A.T;
+        if (left) {
+          const float xi = sm.x[i], yi = sm.y[i];
+          const bool pred = A.xaxis ? (xi > A.meanx) : (yi > A.meany);
+          if (!pred) {
+            const uint32_t j = sm.lt[A.start + ((uint32_t)sm.F[i] - (uint32_t)sm.F[A.start])];
+            const uint32_t oi = sm.ord[i];
+            sm.x[i] = sm.x[j]; sm.y[i] = sm.y[j]; sm.ord[i] = sm.ord[j];
+            sm.x[j] = xi; sm.y[j] = yi; sm.ord[j] = oi;
+          }
+        }
+        sm.seg[i] = (uint16_t)A.slot[left ? 0 : 1];
+      }
+      __syncthreads();
+    }
+    for (uint32_t i = tid; i < L; i += kSubThreads) W.order[s0 + i] = sm.ord[i];
+  }
 }
 
 // ---- subtree sizes, atomic bottom-up -----------------------------------------------------------------

@@ -171,42 +171,53 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
   cudaStream_t st = c->stream;
   BodyArrays &b = c->body[c->cur];
   BvhWork &W = c->bw;
-  const unsigned long long l0 = g_launches;
   bvh_init_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, c->meta, b.x, b.y, n);
   g_launches += 1;
   const uint32_t scan_blocks = cdiv(n, (uint32_t)kScanTile);
-  int level = 0;
-  for (; level < kBvhMaxLevels; ++level) {
-    NB_CUDA(c, cudaMemcpyAsync(c->h_bmeta, W.meta, sizeof(BvhMeta), cudaMemcpyDeviceToHost, st));
-    NB_CUDA(c, cudaStreamSynchronize(st));
-    const uint32_t nbig = c->h_bmeta->cnt_big[level], nsmall = c->h_bmeta->cnt_small[level];
-    if (nbig + nsmall == 0) break;
-    if (c->h_bmeta->n_nodes + 2 * (nbig + nsmall) > W.node_cap)
-      return fail(c, NB_ERR_OVERFLOW, "BVH node pool too small");
-    if (nsmall) bvh_fold_small_kernel<<<std::min(cdiv(nsmall, 8u), (uint32_t)kSMs * 8u), 256, 0, st>>>(W, level);
-    if (nbig) {
-      // tiles of one node are spread over blockIdx.y; with many nodes one block per node suffices
-      const uint32_t gx = std::min(nbig, (uint32_t)kSMs * 4u);
-      const uint32_t gy = std::max(1u, std::min(64u, cdiv(cdiv(n, (uint32_t)kFoldTile), nbig)));
-      bvh_tile_sum_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
-      bvh_tile_summary_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
-      bvh_fold_resolve_kernel<<<dim3(gx, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
-    }
+  // Level-synchronous part: nodes of more than kBvhSmall bodies.  Every kernel reads its work list from device
+  // memory, so a level can be enqueued blind; the host only has to know WHEN the big nodes run out.  It enqueues
+  // as many levels as the previous build needed without looking, then checks once (one sync per build).
+  auto enqueue_level = [&](int level, uint32_t nbig_bound) {
+    const uint32_t gx = std::max(1u, std::min(nbig_bound, (uint32_t)kSMs * 4u));
+    const uint32_t gy = std::max(1u, std::min(64u, cdiv(cdiv(n, (uint32_t)kFoldTile), gx)));
+    bvh_tile_sum_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+    bvh_tile_summary_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+    bvh_fold_resolve_kernel<<<dim3(gx, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
     bvh_count_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
-    bvh_decide_kernel<<<cdiv(nbig + nsmall, 256), 256, 0, st>>>(W, level, (uint32_t)c->leaf_cap);
+    bvh_decide_kernel<<<cdiv(nbig_bound, 256), 256, 0, st>>>(W, level, (uint32_t)c->leaf_cap);
     bvh_flag_reduce_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
     scan_bsum_kernel<<<1, 1024, 0, st>>>(W.bsum, scan_blocks, nullptr);
     bvh_flag_apply_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
     bvh_publish_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
     bvh_swap_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
-    g_launches += 7 + (nsmall ? 1 : 0) + (nbig ? 3 : 0);
+    g_launches += 10;
+  };
+  // big nodes at a level: at most 2^level, and each holds more than kBvhSmall bodies
+  auto bound = [&](int level) {
+    const uint32_t by_size = n / kBvhSmall + 1u;
+    return level >= 31 ? by_size : std::min(by_size, 1u << level);
+  };
+  int level = 0;
+  if (n > kBvhSmall) {
+    for (; level < (int)c->bvh_levels && level < kBvhMaxLevels; ++level) enqueue_level(level, bound(level));
+    for (;; ++level) {
+      NB_CUDA(c, cudaMemcpyAsync(c->h_bmeta, W.meta, sizeof(BvhMeta), cudaMemcpyDeviceToHost, st));
+      NB_CUDA(c, cudaStreamSynchronize(st));
+      if (c->h_bmeta->n_nodes > W.node_cap) return fail(c, NB_ERR_OVERFLOW, "BVH node pool too small");
+      if (level >= kBvhMaxLevels || c->h_bmeta->cnt_big[level] == 0) break;
+      enqueue_level(level, c->h_bmeta->cnt_big[level]);
+    }
+    // levels that really held big nodes (the blind part may have overshot)
+    int used = 0;
+    while (used < kBvhMaxLevels && c->h_bmeta->cnt_big[used] != 0) ++used;
+    c->bvh_levels = (uint32_t)used;
   }
-  c->bvh_levels = (uint32_t)level;
+  // everything below: one block per small subtree, in shared memory
+  bvh_subtree_kernel<<<kSMs * 2, kSubThreads, sizeof(SubSmem), st>>>(W, (uint32_t)c->leaf_cap);
   bvh_sizes_kernel<<<kSMs * 8, 256, 0, st>>>(W);
   bvh_emit_kernel<<<kSMs * 8, 256, 0, st>>>(W, c->meta, c->T, n);
   tree_finish_kernel<true, 8, true><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, W.order, b.x, b.y, b.m, b.id, c->sbody);
-  g_launches += 3;
-  (void)l0;
+  g_launches += 4;
   NB_CUDA(c, cudaGetLastError());
   c->sorted_in = 0; // the tree order lives in vals[0]
   c->tree_valid = true;
@@ -256,12 +267,16 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
 #define NB_TRAVERSE(EX, CNT)                                                                                  \
   traverse_kernel<EX, CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,          \
                                                           c->cfg.theta, first, count)
+#define NB_TRAVERSE_FAST(CNT)                                                                                     \
+  traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
+                                                           c->cfg.theta, first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
   if (ex && c->counting) NB_TRAVERSE(true, true);
   else if (ex) NB_TRAVERSE(true, false);
-  else if (c->counting) NB_TRAVERSE(false, true);
-  else NB_TRAVERSE(false, false);
+  else if (c->counting) NB_TRAVERSE_FAST(true);
+  else NB_TRAVERSE_FAST(false);
 #undef NB_TRAVERSE
+#undef NB_TRAVERSE_FAST
   NB_CUDA(c, cudaGetLastError());
   return NB_OK;
 }
@@ -445,9 +460,9 @@ void nb_destroy(nb_ctx *c) {
   cudaFree(c->flush_buf);
   if (c->h_meta) cudaFreeHost(c->h_meta);
   if (c->h_bmeta) cudaFreeHost(c->h_bmeta);
-  cudaFree(c->bw.nodes); cudaFree(c->bw.meta);
+  cudaFree(c->bw.nodes); cudaFree(c->bw.meta); cudaFree(c->bw.list_sub);
   for (int i = 0; i < 2; ++i) {
-    cudaFree(c->bw.list_big[i]); cudaFree(c->bw.list_small[i]);
+    cudaFree(c->bw.list_big[i]);
     cudaFree(c->tiles.sum[i]); cudaFree(c->tiles.guess[i]);
   }
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -539,10 +554,11 @@ nb_ctx *nb_create(const nb_config *cfg) {
     const size_t lcap = na / 64 + 1024;
     for (int i = 0; i < 2; ++i) {
       NB_TRY(dmalloc(&W.list_big[i], lcap));
-      NB_TRY(dmalloc(&W.list_small[i], lcap));
     }
+    NB_TRY(dmalloc(&W.list_sub, lcap));
     NB_TRY(dmalloc(&W.meta, 1));
     NB_TRY(cudaMallocHost((void **)&c->h_bmeta, sizeof(BvhMeta)));
+    NB_TRY(cudaFuncSetAttribute(bvh_subtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SubSmem)));
     const size_t slots = (na >> kTileSlotShift) + 8;
     for (int i = 0; i < 2; ++i) {
       NB_TRY(dmalloc(&c->tiles.sum[i], slots));
