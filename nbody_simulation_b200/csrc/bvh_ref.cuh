@@ -100,25 +100,27 @@ __global__ void __launch_bounds__(256) bvh_init_kernel(BvhWork W, Meta *meta, co
 }
 
 // ---- fold, big nodes -------------------------------------------------------------------------------------
-// The exact sequential sum of a long slice (seqfold_core.h) in three launches per level:
-//   tile_sum      every 8192-addend tile of every big node: its plain fp64 sum (any order);
-//   tile_summary  the fp64 prefix of the tiles before it tells a tile, to ~1e-4, what the f32 accumulator
-//                 will be when the fold reaches it, i.e. its BINADE; the tile's composed parity function is
-//                 evaluated for that binade — all tiles of all nodes in parallel;
-//   resolve       one block per (node, axis) walks the tiles in order with the true accumulator: a tile whose
-//                 guess holds (same binade, accumulator stays inside it) costs O(1); the others — tile 0 and
-//                 the ~1 tile per power of two the sum crosses — are folded by the block with the windowed
-//                 scan, restarting after each binade change.  Nothing depends on the guess being right.
-constexpr int kFoldThreads = 256;
-constexpr int kFoldChunk = 32;
-constexpr int kFoldTile = kFoldThreads * kFoldChunk; // 8192
-constexpr int kFoldHead = 1024;       // addends at the start of a fold taken by a plain loop
-constexpr uint32_t kTileSlotShift = 12; // slot of a node's tile j = (start >> 12) + j: collision-free for len > 4096
+// The exact sequential f32 sum of a long slice (seqfold_core.h), four launches per level, tiles of 256 addends:
+//   tile_sum      every tile of every big node: its plain fp64 sum (any order), one warp per tile;
+//   tile_prefix   per (node, axis): exclusive fp64 prefix of the tile sums.  It tells a tile, to ~1e-4, what the
+//                 f32 accumulator will be when the fold reaches it, i.e. its BINADE;
+//   tile_summary  the tile's composed parity function for that binade, one warp per tile (8 addends per lane,
+//                 warp scan with compose()) — all tiles of all nodes in parallel;
+//   resolve       one warp per (node, axis) walks the tiles in order with the true accumulator: a run of 32 tiles
+//                 whose guesses hold is applied by one warp scan; a single tile whose guess holds costs O(1); the
+//                 others — tile 0 and the ~1 tile per power of two the sum crosses — are folded plainly (256
+//                 dependent adds fed by shuffles).  Nothing depends on a guess being right.
+constexpr int kFoldTile = 256;
+constexpr uint32_t kTileSlotShift = 7; // slot of a node's tile j = (start >> 7) + j: collision-free for len > 4096
 
 struct TileGuess { // 32 B
   int32_t tot[2], lo[2], hi[2];
   uint32_t key; // biased exponent | sign of the guessed accumulator; 0 = no guess
   uint32_t pad;
+};
+struct TileArrays {
+  double *sum[2];     // [axis][slot]: tile sums, then their exclusive prefix per node
+  TileGuess *guess[2];
 };
 
 __device__ __forceinline__ sf::Summary shfl_up_summary(const sf::Summary &s, int o) {
@@ -131,237 +133,216 @@ __device__ __forceinline__ sf::Summary shfl_up_summary(const sf::Summary &s, int
   }
   return t;
 }
-
-struct FoldSmem {
-  float sx[kFoldTile + kFoldTile / 32]; // index i lives at i + (i >> 5): chunk-strided reads hit distinct banks
-  sf::Summary wsum[kFoldThreads / 32];
-  float acc;
-  uint32_t pos;
-};
-
-// Summaries of the window staged in sm.sx: thread t owns addends [t*cpt, (t+1)*cpt) below wlen.
-// Returns the thread's own summary; `pre` = composition of everything before it; sm.wsum[last] = whole window.
-__device__ __forceinline__ sf::Summary window_scan(FoldSmem &sm, const sf::Binade &b, uint32_t wlen, uint32_t cpt,
-                                                   sf::Summary &pre) {
-  const unsigned tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const uint32_t c0 = tid * cpt;
-  sf::Summary own = sf::identity();
-  bool bad = false;
-  for (uint32_t j = 0; j < cpt; ++j) {
-    const uint32_t i = c0 + j;
-    if (i < wlen) {
-      const sf::QElem q = sf::quantize(sm.sx[i + (i >> 5)], b);
-      bad = bad || q.c == 3;
-      sf::push_fast(own, q.n, q.c); // a bad addend (c == 3) poisons the chunk below
-    }
-  }
-  if (bad) sf::poison(own);
-  sf::Summary inc = own;
+__device__ __forceinline__ sf::Summary warp_scan_summary(sf::Summary inc) { // inclusive, lane order = sequence order
+  const unsigned lane = threadIdx.x & 31;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const sf::Summary t = shfl_up_summary(inc, o);
     if (lane >= (unsigned)o) inc = sf::compose(t, inc);
   }
-  __syncthreads(); // wsum free
-  if (lane == 31) sm.wsum[w] = inc;
-  __syncthreads();
-  if (w == 0) {
-    sf::Summary v = lane < kFoldThreads / 32 ? sm.wsum[lane] : sf::identity();
-#pragma unroll
-    for (int o = 1; o < kFoldThreads / 32; o <<= 1) {
-      const sf::Summary t = shfl_up_summary(v, o);
-      if (lane >= (unsigned)o) v = sf::compose(t, v);
-    }
-    if (lane < kFoldThreads / 32) sm.wsum[lane] = v; // inclusive over warps
-  }
-  __syncthreads();
-  pre = shfl_up_summary(inc, 1);
-  if (lane == 0) pre = sf::identity();
-  if (w > 0) pre = sf::compose(sm.wsum[w - 1], pre);
-  return own;
+  return inc;
+}
+__device__ __forceinline__ sf::Summary guess_summary(const TileGuess &g) {
+  sf::Summary S;
+  S.tot[0] = g.tot[0]; S.tot[1] = g.tot[1];
+  S.lo[0] = g.lo[0]; S.lo[1] = g.lo[1];
+  S.hi[0] = g.hi[0]; S.hi[1] = g.hi[1];
+  return S;
 }
 
-// acc folded over x[0..len), exactly as the sequential loop would, by the whole block.  `consumed` = addends the
-// fold saw before x[0]: early in a fold the sum doubles (changes binade) every few addends, so windows start small.
-__device__ float block_seqfold(FoldSmem &sm, const float *__restrict__ x, uint32_t len, float acc0, uint32_t consumed) {
-  const unsigned tid = threadIdx.x;
-  __syncthreads();
-  if (consumed == 0) {
-    // the first addends change the binade every few steps (the sum doubles): one thread folds them plainly
-    const uint32_t head = min(len, (uint32_t)kFoldHead);
-    for (uint32_t i = tid; i < head; i += kFoldThreads) sm.sx[i] = x[i];
-    __syncthreads();
-    if (tid == 0) {
-      float a = acc0;
-      uint32_t i = 0;
-      for (; i + 8 <= head; i += 8) {
-        float v[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = sm.sx[i + k];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) a = __fadd_rn(a, v[k]);
-      }
-      for (; i < head; ++i) a = __fadd_rn(a, sm.sx[i]);
-      sm.acc = a;
-      sm.pos = head;
-    }
-  } else if (tid == 0) { sm.acc = acc0; sm.pos = 0; }
-  __syncthreads();
-  for (;;) {
-    const float acc = sm.acc;
-    const uint32_t pos = sm.pos;
-    if (pos >= len) return acc;
-    sf::Binade b;
-    if (!sf::binade_of(acc, b)) { // zero / subnormal / non-finite accumulator: one plain step
-      __syncthreads();
-      if (tid == 0) { sm.acc = __fadd_rn(acc, x[pos]); sm.pos = pos + 1; }
-      __syncthreads();
-      continue;
-    }
-    const uint32_t grow = max((uint32_t)kFoldThreads, 2u * (consumed + pos));
-    const uint32_t wlen = min(min((uint32_t)kFoldTile, len - pos), grow);
-    const uint32_t cpt = (wlen + kFoldThreads - 1) / kFoldThreads;
-    for (uint32_t i = tid; i < wlen; i += kFoldThreads) sm.sx[i + (i >> 5)] = x[pos + i];
-    __syncthreads();
-    sf::Summary pre;
-    const sf::Summary own = window_scan(sm, b, wlen, cpt, pre);
-    const int p0 = b.A & 1;
-    const int32_t Ain = b.A + pre.tot[p0];
-    const bool bad = sf::valid_from(pre, b.A) && !sf::valid_from(own, Ain);
-    const int any_bad = __syncthreads_or(bad);
-    if (!any_bad) {
-      if (tid == 0) {
-        sm.acc = sf::binade_value(b, b.A + sm.wsum[kFoldThreads / 32 - 1].tot[p0]);
-        sm.pos = pos + wlen;
-      }
-    } else if (bad) { // the first chunk in which the accumulator leaves the binade: walk it
-      int32_t Ar = Ain;
-      for (uint32_t j = 0; j < cpt; ++j) {
-        const uint32_t i = tid * cpt + j;
-        const float xv = sm.sx[i + (i >> 5)];
-        const sf::QElem q = sf::quantize(xv, b);
-        if (!sf::step_valid(q, Ar)) {
-          sm.acc = __fadd_rn(sf::binade_value(b, Ar), xv);
-          sm.pos = pos + i + 1;
-          break;
-        }
-        Ar = sf::step_apply(q, Ar);
-      }
-    }
-    __syncthreads();
-  }
-}
-
-struct TileArrays {
-  double *sum[2];     // [axis][slot]
-  TileGuess *guess[2];
+// work decomposition shared by the tile kernels: blockIdx.x strides the big-node list, the warps of
+// (blockIdx.y, threadIdx.x / 32) stride the node's tiles, blockIdx.z is the axis
+struct TileIter {
+  uint32_t s, len, ntiles, slot0;
 };
+__device__ __forceinline__ TileIter tile_iter(const BvhWork &W, uint32_t ni) {
+  TileIter t;
+  t.s = W.nodes[ni].start;
+  t.len = W.nodes[ni].len;
+  t.ntiles = (t.len + kFoldTile - 1) / kFoldTile;
+  t.slot0 = t.s >> kTileSlotShift;
+  return t;
+}
 
-__global__ void __launch_bounds__(kFoldThreads) bvh_tile_sum_kernel(BvhWork W, TileArrays TA, int level) {
-  __shared__ double red[kFoldThreads / 32];
+__global__ void __launch_bounds__(256) bvh_tile_sum_kernel(BvhWork W, TileArrays TA, int level) {
   const uint32_t cnt = W.meta->cnt_big[level];
   const uint32_t *list = W.list_big[level & 1];
   const int dim = blockIdx.z;
   const float *src = dim ? W.wy : W.wx;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t w0 = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5), nw = gridDim.y * (blockDim.x >> 5);
   for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
-    const uint32_t ni = list[a];
-    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
-    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
-    for (uint32_t j = blockIdx.y; j + 1 < ntiles; j += gridDim.y) { // the last tile's sum is never needed
-      const float *x = src + s + (size_t)j * kFoldTile;
+    const TileIter t = tile_iter(W, list[a]);
+    for (uint32_t j = w0; j + 1 < t.ntiles; j += nw) { // the last tile's sum is never needed
+      const float *x = src + t.s + (size_t)j * kFoldTile;
       double v = 0.0;
 #pragma unroll 8
-      for (uint32_t i = threadIdx.x; i < (uint32_t)kFoldTile; i += kFoldThreads) v += (double)x[i];
+      for (int i = 0; i < kFoldTile / 32; ++i) v += (double)x[i * 32 + lane];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      __syncthreads();
-      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int k = 0; k < kFoldThreads / 32; ++k) t += red[k];
-        TA.sum[dim][slot0 + j] = t;
-      }
+      if (lane == 0) TA.sum[dim][t.slot0 + j] = v;
     }
   }
 }
 
-__global__ void __launch_bounds__(kFoldThreads) bvh_tile_summary_kernel(BvhWork W, TileArrays TA, int level) {
-  __shared__ FoldSmem sm;
-  __shared__ double red[kFoldThreads / 32];
+// one warp per (node, axis): tile sums -> exclusive prefix, in place
+__global__ void __launch_bounds__(64) bvh_tile_prefix_kernel(BvhWork W, TileArrays TA, int level) {
+  const uint32_t cnt = W.meta->cnt_big[level];
+  const uint32_t *list = W.list_big[level & 1];
+  const int dim = threadIdx.x >> 5;
+  const unsigned lane = threadIdx.x & 31;
+  for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
+    const TileIter t = tile_iter(W, list[a]);
+    double carry = 0.0;
+    auto fetch = [&](uint32_t base) { // the next group's sums are in flight while this one is scanned
+      const uint32_t j = base + lane;
+      return (j + 1 < t.ntiles) ? TA.sum[dim][t.slot0 + j] : 0.0;
+    };
+    double v = fetch(0);
+    for (uint32_t base = 0; base < t.ntiles; base += 32) {
+      const uint32_t j = base + lane;
+      const double vnext = fetch(base + 32);
+      double inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const double u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= (unsigned)o) inc += u;
+      }
+      if (j < t.ntiles) TA.sum[dim][t.slot0 + j] = carry + (inc - v);
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+      v = vnext;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) bvh_tile_summary_kernel(BvhWork W, TileArrays TA, int level) {
+  __shared__ float stage[8][kFoldTile + kFoldTile / 32]; // index i at i + (i >> 5): spreads the lane-strided reads
   const uint32_t cnt = W.meta->cnt_big[level];
   const uint32_t *list = W.list_big[level & 1];
   const int dim = blockIdx.z;
   const float *src = dim ? W.wy : W.wx;
+  const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float *sx = stage[wib];
+  const uint32_t w0 = blockIdx.y * (blockDim.x >> 5) + wib, nw = gridDim.y * (blockDim.x >> 5);
   for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
-    const uint32_t ni = list[a];
-    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
-    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
-    for (uint32_t j = 1 + blockIdx.y; j < ntiles; j += gridDim.y) {
-      // fp64 prefix of the tiles before j
-      double v = 0.0;
-      for (uint32_t k = threadIdx.x; k < j; k += kFoldThreads) v += TA.sum[dim][slot0 + k];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      __syncthreads();
-      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-      __syncthreads();
-      double P = 0.0;
-      for (int k = 0; k < kFoldThreads / 32; ++k) P += red[k];
+    const TileIter t = tile_iter(W, list[a]);
+    for (uint32_t j = 1 + w0; j < t.ntiles; j += nw) {
       sf::Binade b;
       TileGuess g{};
-      if (sf::binade_of(__double2float_rn(P), b)) { // uniform across the block
-        const uint32_t tlen = min((uint32_t)kFoldTile, len - j * kFoldTile);
-        const float *x = src + s + (size_t)j * kFoldTile;
-        for (uint32_t i = threadIdx.x; i < tlen; i += kFoldThreads) sm.sx[i + (i >> 5)] = x[i];
-        __syncthreads();
-        sf::Summary pre;
-        window_scan(sm, b, tlen, kFoldChunk, pre);
-        const sf::Summary all = sm.wsum[kFoldThreads / 32 - 1];
+      if (sf::binade_of(__double2float_rn(TA.sum[dim][t.slot0 + j]), b)) { // warp-uniform
+        const uint32_t tlen = min((uint32_t)kFoldTile, t.len - j * kFoldTile);
+        const float *x = src + t.s + (size_t)j * kFoldTile;
+        __syncwarp();
+        for (uint32_t i = lane; i < tlen; i += 32) sx[i + (i >> 5)] = x[i];
+        __syncwarp();
+        sf::Summary own = sf::identity();
+        bool bad = false;
+#pragma unroll
+        for (uint32_t k = 0; k < (uint32_t)kFoldTile / 32; ++k) {
+          const uint32_t i = lane * (kFoldTile / 32) + k;
+          if (i < tlen) {
+            const sf::QElem q = sf::quantize(sx[i + (i >> 5)], b);
+            bad = bad || q.c == 3;
+            sf::push_fast(own, q.n, q.c); // a bad addend (c == 3) poisons the chunk below
+          }
+        }
+        if (bad) sf::poison(own);
+        const sf::Summary all = warp_scan_summary(own);
         g.tot[0] = all.tot[0]; g.tot[1] = all.tot[1];
         g.lo[0] = all.lo[0]; g.lo[1] = all.lo[1];
         g.hi[0] = all.hi[0]; g.hi[1] = all.hi[1];
         g.key = b.E | b.sign;
       }
-      if (threadIdx.x == 0) TA.guess[dim][slot0 + j] = g;
-      __syncthreads();
+      if (lane == 31) TA.guess[dim][t.slot0 + j] = g;
     }
   }
 }
 
-__global__ void __launch_bounds__(kFoldThreads) bvh_fold_resolve_kernel(BvhWork W, TileArrays TA, int level) {
-  __shared__ FoldSmem sm;
+// plain sequential fold of x[0..len), len <= kFoldTile, into acc by one warp: the whole tile is fetched into
+// registers first (one memory latency, coalesced), then the dependent chain is fed by shuffles
+__device__ __forceinline__ float warp_plain_fold(const float *__restrict__ x, uint32_t len, float acc) {
+  const unsigned lane = threadIdx.x & 31;
+  float v[kFoldTile / 32];
+#pragma unroll
+  for (int i = 0; i < kFoldTile / 32; ++i) v[i] = (uint32_t)(i * 32) + lane < len ? x[i * 32 + lane] : 0.f;
+  if (len == (uint32_t)kFoldTile) {
+#pragma unroll
+    for (int i = 0; i < kFoldTile / 32; ++i) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, v[i], j));
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kFoldTile / 32; ++i) {
+      const uint32_t c = len > (uint32_t)(i * 32) ? min(32u, len - i * 32) : 0u;
+      for (uint32_t j = 0; j < c; ++j) acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, v[i], j));
+    }
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(64) bvh_fold_resolve_kernel(BvhWork W, TileArrays TA, int level) {
   const uint32_t cnt = W.meta->cnt_big[level];
   const uint32_t *list = W.list_big[level & 1];
-  const int dim = blockIdx.y;
+  const int dim = threadIdx.x >> 5;
+  const unsigned lane = threadIdx.x & 31;
   const float *src = dim ? W.wy : W.wx;
   for (uint32_t a = blockIdx.x; a < cnt; a += gridDim.x) {
     const uint32_t ni = list[a];
-    const uint32_t s = W.nodes[ni].start, len = W.nodes[ni].len;
-    const uint32_t ntiles = (len + kFoldTile - 1) / kFoldTile, slot0 = s >> kTileSlotShift;
-    float acc = 0.f;
-    for (uint32_t j = 0; j < ntiles; ++j) {
-      bool fast = false;
+    const TileIter t = tile_iter(W, ni);
+    auto fetch = [&](uint32_t base) { // the next group's guesses are in flight while this one is applied
+      TileGuess g{};
+      if (base + lane < t.ntiles) g = TA.guess[dim][t.slot0 + base + lane];
+      return g;
+    };
+    TileGuess gn = fetch(1);
+    float acc = warp_plain_fold(src + t.s, min((uint32_t)kFoldTile, t.len), 0.f); // tile 0: a new binade every few addends
+    for (uint32_t base = 1; base < t.ntiles; base += 32) {
+      const uint32_t j = base + lane;
+      const TileGuess g = gn;
+      gn = fetch(base + 32);
+      const sf::Summary mine = j < t.ntiles ? guess_summary(g) : sf::identity();
+      const uint32_t cntg = min(32u, t.ntiles - base);
       sf::Binade b;
-      if (j > 0 && sf::binade_of(acc, b)) {
-        const TileGuess g = TA.guess[dim][slot0 + j];
-        if (g.key == (b.E | b.sign)) {
-          sf::Summary S;
-          S.tot[0] = g.tot[0]; S.tot[1] = g.tot[1];
-          S.lo[0] = g.lo[0]; S.lo[1] = g.lo[1];
-          S.hi[0] = g.hi[0]; S.hi[1] = g.hi[1];
-          if (sf::valid_from(S, b.A)) {
-            acc = sf::binade_value(b, b.A + S.tot[b.A & 1]);
-            fast = true;
+      // the whole group at once: every guess names the accumulator's binade and the composition stays inside it
+      bool done = false;
+      if (sf::binade_of(acc, b)) {
+        const bool match = j >= t.ntiles || g.key == (b.E | b.sign);
+        if (__all_sync(0xffffffffu, match)) {
+          const sf::Summary inc = warp_scan_summary(mine);
+          sf::Summary all;
+#pragma unroll
+          for (int p = 0; p < 2; ++p) {
+            all.tot[p] = __shfl_sync(0xffffffffu, inc.tot[p], 31);
+            all.lo[p] = __shfl_sync(0xffffffffu, inc.lo[p], 31);
+            all.hi[p] = __shfl_sync(0xffffffffu, inc.hi[p], 31);
+          }
+          if (sf::valid_from(all, b.A)) {
+            acc = sf::binade_value(b, b.A + all.tot[b.A & 1]);
+            done = true;
           }
         }
       }
-      if (!fast)
-        acc = block_seqfold(sm, src + s + (size_t)j * kFoldTile, min((uint32_t)kFoldTile, len - j * kFoldTile), acc,
-                            j * kFoldTile);
+      if (done) continue;
+      for (uint32_t k = 0; k < cntg; ++k) { // tile by tile
+        const uint32_t key = __shfl_sync(0xffffffffu, g.key, k);
+        sf::Summary S;
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          S.tot[p] = __shfl_sync(0xffffffffu, mine.tot[p], k);
+          S.lo[p] = __shfl_sync(0xffffffffu, mine.lo[p], k);
+          S.hi[p] = __shfl_sync(0xffffffffu, mine.hi[p], k);
+        }
+        if (sf::binade_of(acc, b) && key == (b.E | b.sign) && sf::valid_from(S, b.A)) {
+          acc = sf::binade_value(b, b.A + S.tot[b.A & 1]);
+        } else {
+          const uint32_t jj = base + k;
+          acc = warp_plain_fold(src + t.s + (size_t)jj * kFoldTile, min((uint32_t)kFoldTile, t.len - jj * kFoldTile), acc);
+        }
+      }
     }
-    if (threadIdx.x == 0) {
-      const float mean = __fdiv_rn(acc, __uint2float_rn(len)); // `points.len() as f32`, bvh_tree.rs:67
+    if (lane == 0) {
+      const float mean = __fdiv_rn(acc, __uint2float_rn(t.len)); // `points.len() as f32`, bvh_tree.rs:67
       if (dim) { W.nodes[ni].meany = mean; W.nodes[ni].cy = 0; }
       else { W.nodes[ni].meanx = mean; W.nodes[ni].cx = 0; }
     }
@@ -599,12 +580,25 @@ __global__ void __launch_bounds__(kSubThreads) bvh_subtree_kernel(BvhWork W, uin
       if (tid == 0) sm.nact[cur ^ 1] = 0;
       __syncthreads();
       // count (bvh_tree.rs:70-72)
-      for (uint32_t i = tid; i < L; i += kSubThreads) {
-        const uint32_t a = sm.seg[i];
-        if (a == kSubSettled) continue;
-        SubAct &A = sm.act[cur][a];
-        if (sm.x[i] > A.meanx) atomicAdd(&A.cx, 1u);
-        if (sm.y[i] > A.meany) atomicAdd(&A.cy, 1u);
+      for (uint32_t i0 = warp * 32; i0 < L; i0 += kSubThreads) { // a warp's 32 bodies mostly share one node
+        const uint32_t i = i0 + lane;
+        uint32_t a = i < L ? sm.seg[i] : kSubSettled;
+        bool gx = false, gy = false;
+        if (a != kSubSettled) {
+          gx = sm.x[i] > sm.act[cur][a].meanx;
+          gy = sm.y[i] > sm.act[cur][a].meany;
+        }
+        const uint32_t first = __shfl_sync(0xffffffffu, a, 0);
+        if (__all_sync(0xffffffffu, a == first)) {
+          const uint32_t bx = __popc(__ballot_sync(0xffffffffu, gx)), by = __popc(__ballot_sync(0xffffffffu, gy));
+          if (lane == 0 && first != kSubSettled) {
+            if (bx) atomicAdd(&sm.act[cur][first].cx, bx);
+            if (by) atomicAdd(&sm.act[cur][first].cy, by);
+          }
+        } else if (a != kSubSettled) {
+          if (gx) atomicAdd(&sm.act[cur][a].cx, 1u);
+          if (gy) atomicAdd(&sm.act[cur][a].cy, 1u);
+        }
       }
       __syncthreads();
       // decide (bvh_tree.rs:69-88)

@@ -178,11 +178,13 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
   // memory, so a level can be enqueued blind; the host only has to know WHEN the big nodes run out.  It enqueues
   // as many levels as the previous build needed without looking, then checks once (one sync per build).
   auto enqueue_level = [&](int level, uint32_t nbig_bound) {
-    const uint32_t gx = std::max(1u, std::min(nbig_bound, (uint32_t)kSMs * 4u));
-    const uint32_t gy = std::max(1u, std::min(64u, cdiv(cdiv(n, (uint32_t)kFoldTile), gx)));
-    bvh_tile_sum_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
-    bvh_tile_summary_kernel<<<dim3(gx, gy, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
-    bvh_fold_resolve_kernel<<<dim3(gx, 2), kFoldThreads, 0, st>>>(W, c->tiles, level);
+    const uint32_t gx = std::max(1u, std::min(nbig_bound, (uint32_t)kSMs * 8u));
+    // the warps of gy blocks share one node's tiles; with many nodes one block per node suffices
+    const uint32_t gy = std::max(1u, std::min(128u, cdiv(cdiv(n, (uint32_t)kFoldTile * 8u), gx)));
+    bvh_tile_sum_kernel<<<dim3(gx, gy, 2), 256, 0, st>>>(W, c->tiles, level);
+    bvh_tile_prefix_kernel<<<gx, 64, 0, st>>>(W, c->tiles, level);
+    bvh_tile_summary_kernel<<<dim3(gx, gy, 2), 256, 0, st>>>(W, c->tiles, level);
+    bvh_fold_resolve_kernel<<<gx, 64, 0, st>>>(W, c->tiles, level);
     bvh_count_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
     bvh_decide_kernel<<<cdiv(nbig_bound, 256), 256, 0, st>>>(W, level, (uint32_t)c->leaf_cap);
     bvh_flag_reduce_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
@@ -190,7 +192,7 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
     bvh_flag_apply_kernel<<<scan_blocks, kScanThreads, 0, st>>>(W, n, level);
     bvh_publish_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
     bvh_swap_kernel<<<cdiv(n, 256), 256, 0, st>>>(W, n, level);
-    g_launches += 10;
+    g_launches += 11;
   };
   // big nodes at a level: at most 2^level, and each holds more than kBvhSmall bodies
   auto bound = [&](int level) {

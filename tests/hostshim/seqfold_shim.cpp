@@ -3,6 +3,7 @@
 #include "../../nbody_simulation_b200/csrc/seqfold_core.h"
 #include <stddef.h>
 
+#include <algorithm>
 #include <vector>
 // The device kernel's shape (csrc/bvh_ref.cuh block_seqfold): chunk summaries, a Hillis-Steele inclusive
 // scan with compose() (exercises associativity), the first invalid chunk walks.
@@ -50,7 +51,53 @@ static float fold_scan(const float *x, size_t n, float acc, int chunk, int threa
   return acc;
 }
 
+// The device pipeline for big nodes (csrc/bvh_ref.cuh): fp64 tile prefix -> binade guess -> tile summary ->
+// sequential resolve with plain folds where a guess does not hold.  Returns the sum; *plain = tiles folded plainly.
+static float fold_tiles(const float *x, size_t n, int tile, unsigned long long *plain) {
+  using namespace nb::sf;
+  size_t nt = (n + tile - 1) / tile;
+  std::vector<double> pre(nt, 0.0);
+  double run = 0.0;
+  for (size_t j = 0; j < nt; ++j) {
+    pre[j] = run;
+    size_t e = std::min(n, (j + 1) * (size_t)tile);
+    double t = 0.0;
+    for (size_t i = j * tile; i < e; ++i) t += (double)x[i];
+    run += t;
+  }
+  float acc = 0.f;
+  unsigned long long np = 0;
+  for (size_t j = 0; j < nt; ++j) {
+    size_t b0 = j * (size_t)tile, e = std::min(n, b0 + tile);
+    bool fast = false;
+    Binade g, b;
+    if (j > 0 && binade_of((float)pre[j], g) && binade_of(acc, b) && g.E == b.E && g.sign == b.sign) {
+      Summary all = identity();
+      const size_t per = (size_t)tile / 32; // addends per lane, composed in lane order
+      for (size_t c0 = b0; c0 < e; c0 += per) {
+        Summary own = identity();
+        bool bad = false;
+        for (size_t i = c0; i < std::min(e, c0 + per); ++i) {
+          QElem q = quantize(x[i], g);
+          bad = bad || q.c == 3;
+          push_fast(own, q.n, q.c);
+        }
+        if (bad) poison(own);
+        all = compose(all, own);
+      }
+      if (valid_from(all, b.A)) { acc = binade_value(b, b.A + all.tot[b.A & 1]); fast = true; }
+    }
+    if (!fast) {
+      ++np;
+      for (size_t i = b0; i < e; ++i) acc = fadd(acc, x[i]);
+    }
+  }
+  if (plain) *plain = np;
+  return acc;
+}
+
 extern "C" {
+float nbt_fold_tiles(const float *x, size_t n, int tile, unsigned long long *plain) { return fold_tiles(x, n, tile, plain); }
 float nbt_fold_scan(const float *x, size_t n, float acc, int chunk, int threads) {
   return fold_scan(x, n, acc, chunk, threads);
 }

@@ -25,6 +25,8 @@ def shim():
     L.nbt_fold_windowed.restype = ctypes.c_float
     L.nbt_fold_windowed.argtypes = [fp, ctypes.c_size_t, ctypes.c_float, ctypes.c_int, ctypes.c_int,
                                     ctypes.POINTER(ctypes.c_ulonglong)]
+    L.nbt_fold_tiles.restype = ctypes.c_float
+    L.nbt_fold_tiles.argtypes = [fp, ctypes.c_size_t, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
     L.nbt_fold_scan.restype = ctypes.c_float
     L.nbt_fold_scan.argtypes = [fp, ctypes.c_size_t, ctypes.c_float, ctypes.c_int, ctypes.c_int]
     return L
@@ -36,6 +38,9 @@ def both(L, x, acc=0.0, chunk=8, threads=64):
     slow = ctypes.c_ulonglong(0)
     a = np.float32(L.nbt_fold_plain(p, len(x), acc))
     b = np.float32(L.nbt_fold_windowed(p, len(x), acc, chunk, threads, ctypes.byref(slow)))
+    if acc == 0.0:  # the tile pipeline of the big-node fold (fp64 binade guesses, plain fallback), tiles of 256
+        d = np.float32(L.nbt_fold_tiles(p, len(x), 256, None))
+        assert a.view(np.uint32) == d.view(np.uint32) or (np.isnan(a) and np.isnan(d)), "tile pipeline differs"
     c = np.float32(L.nbt_fold_scan(p, len(x), acc, chunk, threads))
     assert b.view(np.uint32) == c.view(np.uint32) or (np.isnan(b) and np.isnan(c)), "scan-shaped variant differs"
     return a, b, slow.value
@@ -83,3 +88,13 @@ def test_nonzero_start_and_negative_accumulator(shim):
     for acc in (-1e7, 3.25, 1e-3, -0.0):
         a, b, _ = both(shim, x, acc)
         assert same(a, b), acc
+
+
+def test_tile_pipeline_rarely_falls_back(shim):
+    # one plain tile per power of two the sum crosses, plus tile 0
+    r = np.random.default_rng(7)
+    x = r.uniform(0, 1e5, 1_000_000).astype(np.float32)
+    plain = ctypes.c_ulonglong(0)
+    v = np.float32(shim.nbt_fold_tiles(x.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), len(x), 256, ctypes.byref(plain)))
+    ref = np.float32(shim.nbt_fold_plain(x.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), len(x), 0.0))
+    assert same(v, ref) and plain.value <= 20, plain.value
