@@ -22,7 +22,7 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ok = True
-    for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH):
+    for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH, nb.NB_TREE_BVH_REF):
         for n in (100_003, 7):
             p = nb.generate_scene(nb.NB_SCENE_TWO_GALAXY, 3, n)
             steps = 5

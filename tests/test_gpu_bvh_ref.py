@@ -110,3 +110,32 @@ def test_bvh_ref_trajectory_is_bit_identical_to_world_update():
     for a, b in ((q["x"], x), (q["y"], y), (q["vx"], vx), (q["vy"], vy), (q["weight"], m)):
         assert np.array_equal(bits(a), bits(b))
     w.close()
+
+
+def test_bvh_ref_coincident_bodies_terminate():
+    # > 64 coincident bodies: BVHTree::from never separates them (the reference overflows its stack; the oracle
+    # stops at depth 4000, the device build at level 96).  Both end in one over-full leaf reached through a chain
+    # of roots whose empty sibling leaves poison their centres of gravity (0/0), so nothing on the chain is ever
+    # accepted and the forces are the plain sums over the same body order: bit-identical.
+    p = scene("disc", 20_000)
+    p["x"][5000:5200] = np.float32(41234.5)
+    p["y"][5000:5200] = np.float32(56789.25)
+    w = nb.World(len(p), theta=0.5, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    ax, ay = w.accel()
+    info = w.tree()["info"]
+    assert info.overflow_leaves >= 1
+    rx, ry, _, _, _ = ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).accel(0.5, literal=True)
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.close()
+
+
+def test_bvh_ref_resize_and_reuse_context():
+    # the blind level count is a hint from the previous build: a context fed a much smaller / larger scene must adapt
+    w = nb.World(300_000, tree=nb.NB_TREE_BVH_REF)
+    for n in (300_000, 900, 120_000):
+        p = scene("plummer", n)
+        w.set_particles(p)
+        w.build_tree()
+        assert_bvh_equal(w.tree(), ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).export(), f"reuse n={n}")
+    w.close()
