@@ -223,6 +223,11 @@ class World:
         arrays["info"] = info
         return arrays
 
+    def generate_on_device(self, scene, seed, n):
+        """Fill the body state on the device (uniform disc / Plummer): no host buffer, no upload."""
+        self._ck(self._L.nb_scene_generate_device(self._ctx, int(scene), int(seed), int(n)))
+        self.n = int(n)
+
     def draw(self, render_h=RENDER_HEIGHT):
         """`draw(particles, frame)` (src/main.rs:41-72) into a headless RGBA8 frame."""
         frame = np.zeros((render_h, render_h, 4), np.uint8)

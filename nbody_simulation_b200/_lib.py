@@ -146,6 +146,7 @@ def load(path=LIB_PATH):
         "nb_comm_owned_range": (C.c_int, [vp, P(C.c_uint64), P(C.c_uint64)]),
         "nb_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, P(C.c_uint64), P(C.c_uint64)]),
         "nb_scene_generate": (C.c_size_t, [C.c_int32, C.c_uint64, C.c_size_t, vp, C.c_size_t]),
+        "nb_scene_generate_device": (C.c_int, [vp, C.c_int32, C.c_uint64, C.c_size_t]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)  # AttributeError if the .so does not export what the header declares

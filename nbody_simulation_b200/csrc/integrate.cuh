@@ -66,6 +66,42 @@ __global__ void __launch_bounds__(256) soa_to_aos_kernel(BodyArrays b, uint32_t 
   *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
 }
 
+// Device-side scene generation for the two big-N bench scenes: the same counter-based draws
+// as csrc/scene.cpp (splitmix64 of (seed, stream, index)), one body per thread, straight into the SoA state —
+// no host buffer, no upload.  fp64 sin/cos/sqrt as on the host; after rounding to f32 the two agree except
+// where a libm result sits within ~1e-16 of an f32 rounding boundary.
+__device__ __forceinline__ unsigned long long scene_mix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__device__ __forceinline__ float scene_u01(unsigned long long seed, uint32_t stream, unsigned long long idx) {
+  const unsigned long long r =
+      scene_mix64(scene_mix64(seed ^ (0xD1B54A32D192ED03ull * (stream + 1))) + idx * 0x9E3779B97F4A7C15ull);
+  return (float)(r >> 40) * (1.0f / 16777216.0f);
+}
+// scene 1: uniform disc (r = 45000 sqrt(u) about (50000, 50000)); scene 2: projected Plummer a = 2000, clipped
+__global__ void __launch_bounds__(256) scene_kernel(int scene, unsigned long long seed, BodyArrays b, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t stream = scene == 1 ? 3u : 4u;
+  const double a = 6.283185307179586 * (double)scene_u01(seed, stream, 2ull * i);
+  const double u = (double)scene_u01(seed, stream, 2ull * i + 1);
+  double r;
+  if (scene == 1) r = 45000.0 * sqrt(u);
+  else {
+    const double v = 0.999 * u;
+    r = 2000.0 * sqrt(v / (1.0 - v));
+  }
+  float x = (float)(50000.0 + r * cos(a)), y = (float)(50000.0 + r * sin(a));
+  if (scene != 1) {
+    if (!(x >= 0.f && x < 100000.f)) x = x < 0.f ? 0.f : 99999.99f;
+    if (!(y >= 0.f && y < 100000.f)) y = y < 0.f ? 0.f : 99999.99f;
+  }
+  b.x[i] = x; b.y[i] = y; b.vx[i] = 0.f; b.vy[i] = 0.f; b.m[i] = 1u; b.id[i] = i;
+}
+
 __global__ void __launch_bounds__(256) set_identity_kernel(uint32_t *id, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) id[i] = i;

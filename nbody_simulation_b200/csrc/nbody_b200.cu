@@ -676,6 +676,21 @@ int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx
   return NB_OK;
 }
 
+int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) {
+  if (!c) return NB_ERR_INVALID;
+  if (scene != NB_SCENE_UNIFORM_DISC && scene != NB_SCENE_PLUMMER)
+    return fail(c, NB_ERR_INVALID, "nb_scene_generate_device: only the uniform disc and the Plummer scene");
+  if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: n > n_max");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->n = (uint32_t)n;
+  c->tree_valid = false;
+  if (n == 0) return NB_OK;
+  scene_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(scene, seed, c->body[c->cur], (uint32_t)n);
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NB_OK;
+}
+
 int nb_get_bodies_aos(nb_ctx *c, nb_particle *bodies, size_t n) {
   if (!c || (!bodies && n)) return NB_ERR_INVALID;
   if (n < c->n) return fail(c, NB_ERR_CAPACITY, "nb_get_bodies: buffer smaller than body count");

@@ -357,12 +357,13 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
 
     uint32_t cur_count = k, parent = l.w;
     while (parent != 0xffffffffu) {
-      __threadfence();
+      const uint4 lp = T.link(parent); // written by the emit kernel: in flight while the fence drains
+      __threadfence();                 // release: this subtree's summaries are visible before the arrival is
       const uint32_t old = atomicAdd(&T.arrive[parent], REF ? 1u : cur_count);
-      const uint4 lp = T.link(parent);
       const uint32_t total = lp.z & kCountMask;
       if (REF ? (old != 1u) : (old + cur_count != total)) break;
-      __threadfence();
+      // acquire side: the children's summaries are read with ld.cg (L2, the coherence point) by loads that are
+      // issued only after the atomic's result decided the branch above — no second fence
       uint32_t pm = 0;
       float bx = 0.f, by = 0.f;
       bool first = true;

@@ -262,3 +262,19 @@ def test_draw_matches_sequential_reference():
                 ref[off, 3] += 10
     assert np.array_equal(frame.reshape(-1, 4), ref)
     w.close()
+
+
+@pytest.mark.parametrize("sc,kind", [("disc", nb.NB_SCENE_UNIFORM_DISC), ("plummer", nb.NB_SCENE_PLUMMER)])
+def test_device_scene_generation_matches_host(sc, kind):
+    # same counter-based draws; the host's and the device's fp64 sin/cos may differ across an f32 rounding
+    # boundary for ~1 value in 1e9: allow one ulp on at most 5 of 2M coordinates, everything else bit-equal
+    n = 1_000_000
+    p = scene(sc, n, seed=7)
+    w = nb.World(n)
+    w.generate_on_device(kind, 7, n)
+    q = w.particles
+    for k in ("x", "y"):
+        d = np.abs(q[k].view(np.int32).astype(np.int64) - p[k].view(np.int32).astype(np.int64))
+        assert d.max() <= 1 and int((d != 0).sum()) <= 5, (k, int(d.max()), int((d != 0).sum()))
+    assert np.array_equal(q["weight"], p["weight"]) and not q["vx"].any() and not q["vy"].any()
+    w.close()
