@@ -485,6 +485,10 @@ nb_ctx *nb_create(const nb_config *cfg) {
     fail(nullptr, NB_ERR_INVALID, "nb_create: leaf_cap must be in [0, 64]");
     return nullptr;
   }
+  if (cfg->tree_kind == NB_TREE_BVH_REF && cfg->leaf_cap != 0 && cfg->leaf_cap != 64) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: NB_TREE_BVH_REF uses the reference's TARGET_POINTS = 64 (leaf_cap 0 or 64)");
+    return nullptr;
+  }
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {

@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import nbody_simulation_b200 as nb
 
 p = nb.generate_scene(nb.NB_SCENE_TWO_GALAXY, 1, 20_001)
-for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH):
+for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH, nb.NB_TREE_BVH_REF):
     for mode in (nb.NB_FORCE_EXACT, nb.NB_FORCE_FAST):
         w = nb.World(len(p), theta=0.5, tree=tree, force_mode=mode)
         w.set_particles(p)
@@ -21,4 +21,8 @@ for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH):
         q = w.particles
         print(tree, mode, int(c.interactions), float(ax.sum()), int(t["info"].n_nodes), int(f.sum()))
         w.close()
+w = nb.World(30_000)
+w.generate_on_device(nb.NB_SCENE_PLUMMER, 3, 30_000)
+w.step(1)
+w.close()
 print("sanitize case done")
