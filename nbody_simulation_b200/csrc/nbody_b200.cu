@@ -218,7 +218,7 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
   bvh_subtree_kernel<<<kSMs * 2, kSubThreads, sizeof(SubSmem), st>>>(W, (uint32_t)c->leaf_cap);
   bvh_sizes_kernel<<<kSMs * 8, 256, 0, st>>>(W);
   bvh_emit_kernel<<<kSMs * 8, 256, 0, st>>>(W, c->meta, c->T, n);
-  tree_finish_kernel<true, 8, true><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, W.order, b.x, b.y, b.m, b.id, c->sbody);
+  tree_finish_kernel<true, 8, true><<<std::max((uint32_t)kSMs * 16u, cdiv(n / 16u, 128u)), 128, 0, st>>>(c->meta, c->T, W.order, b.x, b.y, b.m, b.id, c->sbody);
   g_launches += 4;
   NB_CUDA(c, cudaGetLastError());
   c->sorted_in = 0; // the tree order lives in vals[0]
@@ -250,9 +250,12 @@ int enqueue_build(nb_ctx *c) {
   exclusive_scan_u32(c->nstart, c->nstart, &c->meta->n_in, n, c->sort.bsum, &c->meta->n_nodes, st);
   if (c->quad) tree_emit_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
-  tree_link_kernel<<<kSMs * 8, 256, 0, st>>>(c->meta, c->T);
-  if (c->quad) tree_finish_kernel<false, 8><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
-  else tree_finish_kernel<true, 8><<<kSMs * 16, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  tree_link_kernel<<<std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u)), 256, 0, st>>>(c->meta, c->T);
+  // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
+  // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
+  const uint32_t fin_blocks = std::max((uint32_t)kSMs * 16u, cdiv(n / 2u, 128u)); // measured: 0.38 -> 0.36 ms build at 1M, 2.32 -> 1.91 at 8M
+  if (c->quad) tree_finish_kernel<false, 8><<<fin_blocks, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  else tree_finish_kernel<true, 8><<<fin_blocks, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
   NB_CUDA(c, cudaGetLastError());
   c->tree_valid = true;
   return NB_OK;
