@@ -102,6 +102,16 @@ __global__ void __launch_bounds__(256) scene_kernel(int scene, unsigned long lon
   b.x[i] = x; b.y[i] = y; b.vx[i] = 0.f; b.vy[i] = 0.f; b.m[i] = 1u; b.id[i] = i;
 }
 
+// Slot order -> AoS in the SAME order: what the reference's Vec looks like after BVHTree::from permuted it.
+__global__ void __launch_bounds__(256) soa_to_aos_slot_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const size_t o = 6 * (size_t)s;
+  *reinterpret_cast<float2 *>(aos + o) = make_float2(b.x[s], b.y[s]);
+  *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(b.vx[s], b.vy[s]);
+  *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
+}
+
 __global__ void __launch_bounds__(256) set_identity_kernel(uint32_t *id, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) id[i] = i;

@@ -747,7 +747,10 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
   int rc = do_steps(c, 1, delta, out);
   if (rc != NB_OK) return rc;
-  soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
+  // NB_TREE_BVH_REF: the caller's Vec comes back permuted exactly as BVHTree::from leaves it (main.rs:400 hands
+  // `self.particles.as_mut()` to the build), because that order is what the next call's tree is built from
+  if (c->bvh_ref) soa_to_aos_slot_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
+  else soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
   NB_CUDA(c, cudaGetLastError());
   NB_CUDA(c, cudaMemcpyAsync(bodies, c->aos, n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -139,3 +139,26 @@ def test_bvh_ref_resize_and_reuse_context():
         w.build_tree()
         assert_bvh_equal(w.tree(), ob.Tree(ob.KIND_LITERAL_BVH, p["x"], p["y"], p["weight"]).export(), f"reuse n={n}")
     w.close()
+
+
+def test_bvh_ref_world_update_host_keeps_the_reference_vec_order():
+    # nb_world_update with the Vec on the host: like the reference, the Vec comes back permuted by BVHTree::from,
+    # so calling it repeatedly follows the same trajectory as the resident nb_step loop and as the oracle's World
+    p = scene("default", 0)[:50_000].copy()
+    theta, dt, steps = 0.7, 0.1, 4
+    w = nb.World(len(p), theta=theta, dt=dt, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    host = p.copy()
+    for _ in range(steps):
+        w.update_host(host, dt)
+    ow = ob.OracleWorld(p)
+    for _ in range(steps):
+        ow.update(ob.KIND_LITERAL_BVH, dt, theta)
+    x, y, vx, vy, m = ow.get()  # by original id; the host Vec is in the reference's permuted order: compare as sets
+
+    def canon(a, b, c, d):
+        rows = np.stack([a.view(np.uint32), b.view(np.uint32), c.view(np.uint32), d.view(np.uint32)], axis=1)
+        return rows[np.lexsort(rows.T[::-1])]
+
+    assert np.array_equal(canon(host["x"], host["y"], host["vx"], host["vy"]), canon(x, y, vx, vy))
+    assert not np.array_equal(bits(host["x"]), bits(x))  # and it really is permuted
+    w.close()
