@@ -37,7 +37,8 @@ class NbConfig(C.Structure):
         ("domain_auto", C.c_int32),
         ("force_mode", C.c_int32),
         ("device", C.c_int32),
-        ("reserved", C.c_int32 * 9),
+        ("faithful_index_bug", C.c_int32),
+        ("reserved", C.c_int32 * 8),
     ]
 
 

@@ -34,6 +34,33 @@ __global__ void __launch_bounds__(256) integrate_resort_kernel(const uint32_t *_
   out.id[j] = in.id[s];
 }
 
+// main.rs:398-423 AS SHIPPED (cfg.faithful_index_bug): `acceleration[idx]` was computed for the body at index idx
+// of the Vec BEFORE BVHTree::from permuted it, and is applied to whatever body sits at idx AFTER.  With
+// pos_of_slot the inverse of `order`: the body at tree position j gets the acceleration of the body whose
+// pre-build slot was j.
+__global__ void __launch_bounds__(256) invert_order_kernel(const uint32_t *__restrict__ order, uint32_t n,
+                                                           uint32_t *__restrict__ pos_of_slot) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) pos_of_slot[order[j]] = j;
+}
+__global__ void __launch_bounds__(256) integrate_resort_bug_kernel(const uint32_t *__restrict__ order,
+                                                                   const uint32_t *__restrict__ pos_of_slot,
+                                                                   const float2 *__restrict__ sacc, BodyArrays in,
+                                                                   BodyArrays out, uint32_t n, float dt) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const uint32_t s = order[j];
+  const float2 a = sacc[pos_of_slot[j]];
+  const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
+  const float vy = __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
+  out.vx[j] = vx;
+  out.vy[j] = vy;
+  out.x[j] = __fadd_rn(in.x[s], __fmul_rn(vx, dt));
+  out.y[j] = __fadd_rn(in.y[s], __fmul_rn(vy, dt));
+  out.m[j] = in.m[s];
+  out.id[j] = in.id[s];
+}
+
 // Permute only mass/id for tree positions outside [jfirst, jfirst+jcount) (multi-GPU: the
 // other ranks' bodies arrive by all-gather, mass and id are replicated and permuted locally).
 __global__ void __launch_bounds__(256) permute_mid_kernel(const uint32_t *__restrict__ order, BodyArrays in,

@@ -299,7 +299,12 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   BodyArrays &in = c->body[c->cur], &out = c->body[c->cur ^ 1];
   const uint32_t *order = c->vals[c->sorted_in];
   g_launches += (count ? 1 : 0) + (c->n_ranks > 1 ? 1 : 0);
-  if (count)
+  if (c->cfg.faithful_index_bug && count) { // single GPU, NB_TREE_BVH_REF (checked in nb_create / nb_comm_init)
+    uint32_t *pos_of_slot = c->vals[c->sorted_in ^ 1];
+    invert_order_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, n, pos_of_slot);
+    integrate_resort_bug_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, pos_of_slot, c->sacc, in, out, n, dt);
+    g_launches += 1;
+  } else if (count)
     integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt);
   if (c->n_ranks > 1) {
     permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
@@ -486,6 +491,10 @@ nb_ctx *nb_create(const nb_config *cfg) {
   }
   if (cfg->leaf_cap < 0 || cfg->leaf_cap > 64) {
     fail(nullptr, NB_ERR_INVALID, "nb_create: leaf_cap must be in [0, 64]");
+    return nullptr;
+  }
+  if (cfg->faithful_index_bug && cfg->tree_kind != NB_TREE_BVH_REF) {
+    fail(nullptr, NB_ERR_INVALID, "nb_create: faithful_index_bug reproduces main.rs:398-423 and needs NB_TREE_BVH_REF");
     return nullptr;
   }
   if (cfg->tree_kind == NB_TREE_BVH_REF && cfg->leaf_cap != 0 && cfg->leaf_cap != 64) {
@@ -1011,6 +1020,7 @@ int nb_comm_unique_id(uint8_t id[NB_UNIQUE_ID_BYTES]) {
 int nb_comm_init(nb_ctx *c, int rank, int n_ranks, const uint8_t id[NB_UNIQUE_ID_BYTES]) {
   if (!c || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return NB_ERR_INVALID;
   if (n_ranks == 1) { c->rank = 0; c->n_ranks = 1; return NB_OK; }
+  if (c->cfg.faithful_index_bug) return fail(c, NB_ERR_INVALID, "faithful_index_bug is single-GPU only");
   std::string err;
   if (!g_nccl.load(err)) return fail(c, NB_ERR_NCCL, err);
   NB_CUDA(c, cudaSetDevice(c->device));

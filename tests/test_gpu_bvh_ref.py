@@ -162,3 +162,28 @@ def test_bvh_ref_world_update_host_keeps_the_reference_vec_order():
     assert np.array_equal(canon(host["x"], host["y"], host["vx"], host["vy"]), canon(x, y, vx, vy))
     assert not np.array_equal(bits(host["x"]), bits(x))  # and it really is permuted
     w.close()
+
+
+def test_bvh_ref_faithful_index_bug_matches_the_reference_as_shipped():
+    # main.rs:398-423 verbatim: acceleration[idx] (computed in pre-build Vec order) lands on the body that
+    # BVHTree::from moved to idx.  Behind cfg.faithful_index_bug the device step reproduces exactly that.
+    p = scene("default", 0)[:40_000].copy()
+    theta, dt, steps = 50.0, 0.1, 5
+    w = nb.World(len(p), theta=theta, dt=dt, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT,
+                 faithful_index_bug=True)
+    w.set_particles(p)
+    w.step(steps)
+    ow = ob.OracleWorld(p)
+    for _ in range(steps):
+        ow.update(ob.KIND_LITERAL_BVH, dt, theta, faithful_bug=True)
+    x, y, vx, vy, _ = ow.get()
+    q = w.particles
+    for a, b in ((q["x"], x), (q["y"], y), (q["vx"], vx), (q["vy"], vy)):
+        assert np.array_equal(bits(a), bits(b))
+    # and it is observably different from the identity-order step
+    ref = nb.World(len(p), theta=theta, dt=dt, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    ref.set_particles(p)
+    ref.step(steps)
+    assert not np.array_equal(bits(ref.particles["vx"]), bits(q["vx"]))
+    w.close()
+    ref.close()
