@@ -173,10 +173,10 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 
 // FAST-mode kernel (NB_FORCE_FAST): same walk, same per-lane decisions, written for issue slots.
 //  * accepted interactions are plain predicated code (no vote guard around them);
-//  * a terminal visit runs a warp-uniform body loop, two bodies per trip; lanes that do not take the
-//    leaf (masked, or accepted the twig) and the odd tail use mass 0, which adds exactly 0 — no divergent
-//    branch, no convergence barriers;
-//  * summation order inside a lane is unchanged (tree order).
+//  * a terminal visit runs a warp-uniform body loop, two bodies per trip plus an odd tail; every lane sums
+//    the leaf into a private pair and only the lanes that take it (not masked, did not accept the twig)
+//    add the pair to their acceleration — no divergent branch, no per-body predicate or select;
+//  * a leaf's bodies are summed first and added as one term (FAST mode's tolerance allows the reordering).
 template <bool COUNT, bool CONTAINS>
 __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
                                                    Meta *meta, const float4 *__restrict__ sbody,
@@ -218,20 +218,28 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
         n_inter += (acc ? 1u : 0u) + (take ? k : 0u);
       }
       if (__any_sync(0xffffffffu, take)) {
+        // warp-uniform trip count; every lane sums the leaf into (lx, ly) and only the takers keep it
         const float4 *bp = sbody + l.y;
-        for (uint32_t j = 0; j < k; j += 2) {
+        float lx = 0.f, ly = 0.f;
+        uint32_t j = 0;
+#pragma unroll 2
+        for (; j + 1 < k; j += 2) {
           const float4 b0 = bp[j];
-          const float4 b1 = bp[j + 1]; // sbody is padded; the tail body is given mass 0
-          const float m1 = (j + 1 < k) ? b1.z : 0.f;
-          // uniform trip count; only the accumulating FFMAs are predicated
+          const float4 b1 = bp[j + 1];
           const float dx0 = b0.x - px, dy0 = b0.y - py, dx1 = b1.x - px, dy1 = b1.y - py;
           const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
-          const float w1 = m1 * rcp_approx(fmaf(fabsf(dx1) + fabsf(dy1), fmaxf(fmaf(dy1, dy1, dx1 * dx1), 0.001f), 1e-20f));
-          if (take) {
-            ax = fmaf(dx0, w0, ax); ay = fmaf(dy0, w0, ay);
-            ax = fmaf(dx1, w1, ax); ay = fmaf(dy1, w1, ay);
-          }
+          const float w1 = b1.z * rcp_approx(fmaf(fabsf(dx1) + fabsf(dy1), fmaxf(fmaf(dy1, dy1, dx1 * dx1), 0.001f), 1e-20f));
+          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
+          lx = fmaf(dx1, w1, lx); ly = fmaf(dy1, w1, ly);
         }
+        if (j < k) {
+          const float4 b0 = bp[j];
+          const float dx0 = b0.x - px, dy0 = b0.y - py;
+          const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
+          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
+        }
+        ax += take ? lx : 0.f; // selects, not a branch: the loop body of the walk stays convergent
+        ay += take ? ly : 0.f;
       }
       cur = l.x;
     } else {
