@@ -248,9 +248,11 @@ int enqueue_build(nb_ctx *c) {
   if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
   exclusive_scan_u32(c->nstart, c->nstart, &c->meta->n_in, n, c->sort.bsum, &c->meta->n_nodes, st);
-  if (c->quad) tree_emit_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
+  if (c->quad) tree_emit_quad_kernel<<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
-  tree_link_kernel<<<std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u)), 256, 0, st>>>(c->meta, c->T);
+  const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
+  if (c->quad) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
+  else tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
   // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
   const uint32_t fin_blocks = std::max((uint32_t)kSMs * 16u, cdiv(n / 2u, 128u)); // measured: 0.38 -> 0.36 ms build at 1M, 2.32 -> 1.91 at 8M
@@ -465,7 +467,7 @@ void nb_destroy(nb_ctx *c) {
   for (int i = 0; i < 2; ++i) { cudaFree(c->keys[i]); cudaFree(c->vals[i]); }
   cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.ghist); cudaFree(c->sort.tickets); cudaFree(c->sort.status); cudaFree(c->sort.bsum);
   cudaFree(c->T.box); cudaFree(c->T.node); cudaFree(c->T.mass); cudaFree(c->T.depth);
-  cudaFree(c->T.bmax); cudaFree(c->T.arrive);
+  cudaFree(c->T.bmax); cudaFree(c->T.arrive); cudaFree(c->T.kids);
   cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
   cudaFree(c->flush_buf);
   if (c->h_meta) cudaFreeHost(c->h_meta);
@@ -551,6 +553,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->T.depth, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.bmax, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.arrive, (size_t)c->T.capacity));
+  if (c->quad) NB_TRY(dmalloc(&c->T.kids, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->sbody, na));
   NB_TRY(dmalloc(&c->sacc, na));
   NB_TRY(dmalloc(&c->bounds_partial, (size_t)kSMs * 4));

@@ -37,6 +37,8 @@ struct TreeArrays {
   int32_t *depth;
   float2 *bmax;       // LBVH: max corner (for the bounds union)
   uint32_t *arrive;   // up-sweep arrival counters (bodies arrived per internal node)
+  uint4 *kids;        // quadtree: the (up to 4) children of an internal node in child order, 0xffffffff = none;
+                      // lets the up-sweep fetch all child summaries at once instead of chasing skip links
   uint32_t capacity;  // node pool size
 };
 
@@ -204,7 +206,98 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
   }
 }
 
+// Pass 2 for the quadtree, node-parallel.  Only ~30 % of the bodies start a node, so one thread per body
+// leaves most lanes idle while the starters walk their levels; here a block compacts the nodes its 1024
+// bodies start (block scan of the per-body node counts) and hands them out one per thread.  Each node
+// walks the reference's f32 midline chain (quad_tree.rs:172-194) from the root to its own level — the same
+// operations in the same order as the per-body walk, so the boxes are bit-identical.
+constexpr int kEmitBodies = 1024;
+__global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
+                                                             const uint8_t *__restrict__ leafdepth,
+                                                             const uint32_t *__restrict__ base, TreeArrays T) {
+  const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
+  if (n_nodes > T.capacity) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
+    return;
+  }
+  __shared__ uint32_t s_excl[kEmitBodies];
+  __shared__ int8_t s_c[kEmitBodies];
+  __shared__ uint32_t s_warp[8];
+  const uint32_t b0 = blockIdx.x * (uint32_t)kEmitBodies;
+  if (b0 >= n_in) return;
+  const uint32_t j0 = threadIdx.x * 4u;
+  uint32_t cnt[4];
+  unsigned long long prev = (b0 + j0 > 0 && b0 + j0 - 1 < n_in) ? skeys[b0 + j0 - 1] : 0ull;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const uint32_t i = b0 + j0 + r;
+    cnt[r] = 0;
+    int c = -1;
+    if (i < n_in) {
+      const unsigned long long ki = skeys[i];
+      const int L = leafdepth[i];
+      c = (i > 0) ? cpl<2>(prev, ki) : -1;
+      cnt[r] = (c < L) ? (uint32_t)(L - c) : 0u;
+      prev = ki;
+    }
+    s_c[j0 + r] = (int8_t)c;
+  }
+  const uint32_t mine = cnt[0] + cnt[1] + cnt[2] + cnt[3];
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((threadIdx.x & 31) >= (unsigned)o) inc += v;
+  }
+  if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  uint32_t woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    const uint32_t v = s_warp[w];
+    if ((unsigned)w < (threadIdx.x >> 5)) woff += v;
+    total += v;
+  }
+  uint32_t ex = woff + inc - mine;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    s_excl[j0 + r] = ex;
+    ex += cnt[r];
+  }
+  __syncthreads();
+  const float rx = meta->x0, ry = meta->y0, rh = meta->h;
+  for (uint32_t t = threadIdx.x; t < total; t += blockDim.x) {
+    // owner: the last body whose exclusive count is <= t (bodies starting no node share their successor's value)
+    uint32_t lo = 0, hi = kEmitBodies;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (s_excl[mid] <= t) lo = mid;
+      else hi = mid;
+    }
+    const uint32_t i = b0 + lo, off = t - s_excl[lo];
+    const unsigned long long ki = skeys[i];
+    const int level = (int)s_c[lo] + 1 + (int)off;
+    const bool leaf = (level == (int)leafdepth[i]);
+    float ox = rx, oy = ry, hh = rh;
+    for (int l = 0; l < level; ++l) {
+      hh = __fmul_rn(hh, 0.5f);
+      const float mx = __fadd_rn(ox, hh), my = __fadd_rn(oy, hh);
+      const uint32_t dg = (uint32_t)(ki >> (kKeyBits - 2 * (l + 1))) & 3u;
+      ox = (dg & 1u) ? mx : ox;
+      oy = (dg & 2u) ? my : oy;
+    }
+    const uint32_t e = find_end<2>(skeys, i, ki, level, n_in);
+    const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
+    const uint32_t idx = base[i] + off;
+    T.depth[idx] = level;
+    T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+    T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
+    T.cm(idx) = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
+  }
+}
+
 // Parent links (from the parents' side) + reset of the arrival counters.
+template <bool KIDS>
 __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__ meta, TreeArrays T) {
   if (meta->error) return;
   const uint32_t n_nodes = meta->n_nodes;
@@ -213,12 +306,17 @@ __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__
     const uint4 l = T.link(p);
     if (l.z & kLeafBit) continue;
     bool all_leaf = true;
+    uint32_t kid[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    int q = 0;
     for (uint32_t c = p + 1; c < l.x;) {
       uint32_t *lc = reinterpret_cast<uint32_t *>(&T.link(c));
       lc[3] = p;
       all_leaf = all_leaf && (lc[2] & kLeafBit);
+      if (q < 4) kid[q] = c;
+      ++q;
       c = lc[0];
     }
+    if (KIDS) T.kids[p] = make_uint4(kid[0], kid[1], kid[2], kid[3]);
     // a "twig": opening it means summing every body below it, in tree order (main.rs:351-363)
     if (all_leaf) reinterpret_cast<uint32_t *>(&T.link(p))[2] = l.z | kTwigBit;
   }
@@ -358,6 +456,8 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
     uint32_t cur_count = k, parent = l.w;
     while (parent != 0xffffffffu) {
       const uint4 lp = T.link(parent); // written by the emit kernel: in flight while the fence drains
+      uint4 kd = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+      if (!LBVH && !REF) kd = T.kids[parent]; // written by the link kernel
       __threadfence();                 // release: this subtree's summaries are visible before the arrival is
       const uint32_t old = atomicAdd(&T.arrive[parent], REF ? 1u : cur_count);
       const uint32_t total = lp.z & kCountMask;
@@ -368,6 +468,29 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
       float bx = 0.f, by = 0.f;
       bool first = true;
       float mnx = 3.402823466e+38f, mny = 3.402823466e+38f, mxx = 0.f, mxy = 0.f;
+      if (!LBVH && !REF) {
+        // quadtree: all child summaries are requested at once (child indices from tree_link_kernel), then folded
+        // in child order
+        const uint32_t kid[4] = {kd.x, kd.y, kd.z, kd.w};
+        uint32_t km[4];
+        float4 kc[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (kid[q] != 0xffffffffu) {
+            km[q] = __ldcg(&T.mass[kid[q]]);
+            kc[q] = __ldcg(&T.cm(kid[q]));
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (kid[q] != 0xffffffffu) {
+            const float mf = (float)km[q];
+            bx = __fadd_rn(bx, __fmul_rn(kc[q].x, mf));
+            by = __fadd_rn(by, __fmul_rn(kc[q].y, mf));
+            pm += km[q];
+          }
+        }
+      } else
       for (uint32_t c = parent + 1; c < lp.x;) {
         const uint32_t cm_u = __ldcg(&T.mass[c]);
         const float4 ccm = __ldcg(&T.cm(c));
