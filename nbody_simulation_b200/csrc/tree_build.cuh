@@ -68,30 +68,12 @@ __device__ __forceinline__ uint32_t find_end(const unsigned long long *__restric
   return lo;
 }
 
-// L(i): merge outward over the two monotone neighbour sequences, cap steps.
-template <int BPL>
-__device__ __forceinline__ int leaf_depth_of(const unsigned long long *__restrict__ skeys, uint32_t i,
-                                             unsigned long long ki, uint32_t n_in, int cap) {
-  constexpr int D = kKeyBits / BPL;
-  int l = (int)i - 1, r = (int)i + 1;
-  int cl = (l >= 0) ? cpl<BPL>(skeys[l], ki) : -1;
-  int cr = (r < (int)n_in) ? cpl<BPL>(skeys[r], ki) : -1;
-  int c = -1;
-  for (int s = 0; s < cap; ++s) {
-    if (cl < 0 && cr < 0) { c = -1; break; }
-    if (cl >= cr) {
-      c = cl;
-      --l;
-      cl = (l >= 0) ? cpl<BPL>(skeys[l], ki) : -1;
-    } else {
-      c = cr;
-      ++r;
-      cr = (r < (int)n_in) ? cpl<BPL>(skeys[r], ki) : -1;
-    }
-  }
-  int L = c + 1;
-  return L > D ? D : L;
-}
+// L(i) by sliding window: at least cap other bodies share a depth-d prefix with body i  <=>  some window of
+// cap+1 CONSECUTIVE sorted bodies that contains i has a common prefix of >= d levels, and a window's common
+// prefix is cpl(first, last).  So (cap-th largest cpl(i,j)) = max over j in [i-cap, i] of cpl(k[j], k[j+cap])
+// (windows clipped to [0, n_in); none => -1).  A block stages its keys plus a halo of cap on either side in
+// shared memory, forms the window prefixes once and every body takes the maximum over its cap+1 windows.
+constexpr int kCapMax = 64; // nb_create bounds leaf_cap by this
 
 // Pass 1: L(i) and the number of nodes body i starts.
 template <int BPL, bool COMPRESS>
@@ -99,13 +81,31 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
                                                          int cap, uint8_t *__restrict__ leafdepth,
                                                          uint32_t *__restrict__ nstart) {
   const uint32_t n_in = meta->n_in;
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i0 = blockIdx.x * blockDim.x;
+  const uint32_t i = i0 + threadIdx.x;
+  __shared__ unsigned long long s_k[256 + 2 * kCapMax]; // keys of positions i0 - cap .. i0 + 255 + cap
+  __shared__ int8_t s_w[256 + kCapMax];                 // common prefix of the window starting at i0 - cap + t
+  for (int t = threadIdx.x; t < 256 + 2 * cap; t += 256) {
+    const long long p = (long long)i0 - cap + t;
+    s_k[t] = (p >= 0 && p < (long long)n_in) ? skeys[p] : 0ull;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < 256 + cap; t += 256) {
+    const long long j = (long long)i0 - cap + t;
+    s_w[t] = (j >= 0 && j + cap < (long long)n_in) ? (int8_t)cpl<BPL>(s_k[t], s_k[t + cap]) : (int8_t)-1;
+  }
+  __syncthreads();
   uint32_t cnt = 0, isleaf = 0, over = 0;
   int L = 0, statdepth = 0;
   if (i < n_in) {
-    const unsigned long long ki = skeys[i];
-    L = leaf_depth_of<BPL>(skeys, i, ki, n_in, cap);
-    const int c = (i > 0) ? cpl<BPL>(skeys[i - 1], ki) : -1;
+    const unsigned long long ki = s_k[threadIdx.x + cap];
+    int cc = -1;
+    for (int q = 0; q <= cap; ++q) {
+      const int w = s_w[threadIdx.x + q];
+      cc = w > cc ? w : cc;
+    }
+    L = cc + 1 > kKeyBits / BPL ? kKeyBits / BPL : cc + 1;
+    const int c = (i > 0) ? cpl<BPL>(s_k[threadIdx.x + cap - 1], ki) : -1;
     leafdepth[i] = (uint8_t)L;
     statdepth = L;
     if (c < L) {
