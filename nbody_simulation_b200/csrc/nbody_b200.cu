@@ -257,7 +257,8 @@ int enqueue_build(nb_ctx *c) {
   // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
   const uint32_t fin_blocks = std::max((uint32_t)kSMs * 16u, cdiv(n / 2u, 128u)); // measured: 0.38 -> 0.36 ms build at 1M, 2.32 -> 1.91 at 8M
   if (c->quad) tree_finish_kernel<false, 8><<<fin_blocks, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
-  else tree_finish_kernel<true, 8><<<fin_blocks, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  else // one warp per node: about n / 16 warps (an LBVH of 64-body buckets has ~n / 20 nodes)
+    tree_finish_kernel<true, 8, false, true><<<std::max((uint32_t)kSMs * 16u, cdiv(n / 16u, 4u)), 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
   NB_CUDA(c, cudaGetLastError());
   c->tree_valid = true;
   return NB_OK;

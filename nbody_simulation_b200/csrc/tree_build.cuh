@@ -358,7 +358,11 @@ template <bool LBVH> struct LeafAcc {
 // REF (NB_TREE_BVH_REF, bvh_ref.cuh): the leaf slices keep the order `partition` left them in
 // (bvh_tree.rs:40-54 borrows the slice as is) and a leaf may be EMPTY (cog = 0/0, box = (MAX, -MAX)), so
 // parents are completed by counting arrived children, not bodies.
-template <bool LBVH, int MAXK, bool REF = false>
+// WARP (NB_TREE_LBVH, bucket leaves of up to 64 bodies): one WARP per node instead of one thread.  The warp
+// sorts the leaf's (id, slot) pairs with a 64-element bitonic network over shuffles (two elements per lane),
+// gathers and writes the bodies with all lanes, and lane 0 then folds the leaf IN TREE ORDER from a shared
+// staging row (the f32 sum is order dependent) and climbs alone.
+template <bool LBVH, int MAXK, bool REF = false, bool WARP = false>
 __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ meta, TreeArrays T,
                                                           uint32_t *__restrict__ order, const float *__restrict__ x,
                                                           const float *__restrict__ y, const uint32_t *__restrict__ m,
@@ -373,7 +377,11 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
     const uint32_t mm = m[sl];
     sbody[j] = make_float4(x[sl], y[sl], (float)mm, __uint_as_float(mm));
   }
-  for (uint32_t node = tid; node < n_nodes; node += nth) {
+  const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const uint32_t unit = WARP ? (tid >> 5) : tid, n_units = WARP ? (nth >> 5) : nth;
+  __shared__ float s_bx[WARP ? 4 : 1][64], s_by[WARP ? 4 : 1][64];
+  __shared__ uint32_t s_bm[WARP ? 4 : 1][64];
+  for (uint32_t node = unit; node < n_nodes; node += n_units) {
     const uint4 l = T.link(node);
     if (!(l.z & kLeafBit)) continue;
     const uint32_t s = l.y, k = l.z & kCountMask;
@@ -385,7 +393,54 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
       sbody[s + j] = make_float4(bx, by, (float)mm, __uint_as_float(mm));
       A.add(bx, by, mm);
     };
-    if (REF) {
+    if (WARP && k <= 64) {
+      // element e = r * 32 + lane; padding ids sort to the end
+      uint32_t slot[2], bid[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const uint32_t e = r * 32 + lane;
+        slot[r] = (e < k) ? order[s + e] : 0u;
+        bid[r] = (e < k) ? id[slot[r]] : 0xffffffffu;
+      }
+#pragma unroll
+      for (int size = 2; size <= 64; size <<= 1) {
+#pragma unroll
+        for (int j = size >> 1; j > 0; j >>= 1) {
+          if (j == 32) { // size 64, ascending: the partner is this lane's other element
+            if (bid[0] > bid[1]) {
+              const uint32_t tk = bid[0], tv = slot[0];
+              bid[0] = bid[1]; slot[0] = slot[1];
+              bid[1] = tk; slot[1] = tv;
+            }
+          } else {
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              const bool asc = ((r * 32 + lane) & size) == 0, lower = (lane & j) == 0;
+              const uint32_t pk = __shfl_xor_sync(0xffffffffu, bid[r], j), pv = __shfl_xor_sync(0xffffffffu, slot[r], j);
+              const bool sw = (asc == lower) ? (pk < bid[r]) : (pk > bid[r]);
+              bid[r] = sw ? pk : bid[r];
+              slot[r] = sw ? pv : slot[r];
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const uint32_t e = r * 32 + lane;
+        if (e < k) {
+          const uint32_t sl = slot[r], mm = m[sl];
+          const float bx = x[sl], by = y[sl];
+          order[s + e] = sl;
+          sbody[s + e] = make_float4(bx, by, (float)mm, __uint_as_float(mm));
+          s_bx[wib][e] = bx; s_by[wib][e] = by; s_bm[wib][e] = mm;
+        }
+      }
+      __syncwarp();
+      if (lane != 0) continue; // the other lanes wait at the next leaf's first shuffle
+      for (uint32_t j = 0; j < k; ++j) A.add(s_bx[wib][j], s_by[wib][j], s_bm[wib][j]);
+    } else if (WARP && lane != 0) {
+      continue;
+    } else if (REF) {
       for (uint32_t j = 0; j < k; ++j) place(j, order[s + j]);
     } else if (k <= (uint32_t)MAXK) { // registers: bubble network, padding keys sort to the end
       uint32_t slot[MAXK], bid[MAXK];
