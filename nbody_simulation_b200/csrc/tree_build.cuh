@@ -338,6 +338,12 @@ __global__ void __launch_bounds__(256) tree_link_kernel(const Meta *__restrict__
 //             (quad_tree.rs:253-266 folds from (0,0); bvh_tree.rs:148-154 is a*m0 + b*m1)
 //   LBVH bounds: tight AABB with min seeded f32::MAX and max seeded 0 (bvh_tree.rs:42,59),
 //             size = max - min, s2 = max(w,h)^2 as main.rs:371 computes it.
+__device__ __forceinline__ uint32_t atomic_add_release(uint32_t *p, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.add.release.gpu.global.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+
 template <bool LBVH> struct LeafAcc {
   float ax = 0.f, ay = 0.f;
   uint32_t mass = 0;
@@ -513,8 +519,9 @@ __global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ met
       const uint4 lp = T.link(parent); // written by the emit kernel: in flight while the fence drains
       uint4 kd = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
       if (!LBVH && !REF) kd = T.kids[parent]; // written by the link kernel
-      __threadfence();                 // release: this subtree's summaries are visible before the arrival is
-      const uint32_t old = atomicAdd(&T.arrive[parent], REF ? 1u : cur_count);
+      // release: this subtree's summaries are visible at GPU scope before the arrival is.  atom.release is
+      // MEMBAR.ALL.GPU + the atomic; __threadfence() would be the stronger MEMBAR.SC.GPU plus an L1 invalidate
+      const uint32_t old = atomic_add_release(&T.arrive[parent], REF ? 1u : cur_count);
       const uint32_t total = lp.z & kCountMask;
       if (REF ? (old != 1u) : (old + cur_count != total)) break;
       // acquire side: the children's summaries are read with ld.cg (L2, the coherence point) by loads that are
