@@ -497,8 +497,8 @@ __global__ void __launch_bounds__(256) bvh_swap_kernel(BvhWork W, uint32_t n, in
 // ---- small subtrees: one block finishes a node of <= kBvhSmall bodies, all levels below it, in smem -----------
 // Same steps as the level-synchronous kernels above (fold -> count -> decide -> flag scan -> publish -> swap),
 // over the bodies of one subtree held in shared memory; nodes are appended to the global pool.
-constexpr int kSubThreads = 256;
-constexpr int kSubItems = kBvhSmall / kSubThreads; // 16
+constexpr int kSubThreads = 1024; // few subtree roots (n / 4096 .. n / 2048 blocks): wide blocks keep more lanes on each one
+constexpr int kSubItems = kBvhSmall / kSubThreads; // 4
 constexpr uint16_t kSubSettled = 0xffffu;
 
 struct SubAct { // an internal node of the current local level
@@ -712,9 +712,9 @@ __global__ void __launch_bounds__(256) bvh_sizes_kernel(BvhWork W) {
     if (!(W.nodes[v].flags & kBNodeLeaf)) continue;
     uint32_t p = W.nodes[v].parent;
     while (p != 0xffffffffu) {
-      __threadfence();
-      if (atomicAdd(&W.nodes[p].arrive, 1u) == 0u) break; // the second child to arrive owns the parent
-      __threadfence();
+      // release: this child's size is visible before its arrival; the owner's ld.cg loads below are issued only
+      // after the atomic's result decided the branch (same protocol as tree_finish_kernel)
+      if (atomic_add_release(&W.nodes[p].arrive, 1u) == 0u) break; // the second child to arrive owns the parent
       const uint32_t c0 = W.nodes[p].child0;
       const uint32_t sz = 1u + __ldcg(&W.nodes[c0].size) + __ldcg(&W.nodes[c0 + 1].size);
       W.nodes[p].size = sz;
