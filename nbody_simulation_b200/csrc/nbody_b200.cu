@@ -97,7 +97,7 @@ struct nb_ctx {
   uint32_t *vals[2]{};
   int sorted_in = 0; // keys[sorted_in] / vals[sorted_in] hold the sorted keys / tree order
   uint8_t *leafdepth = nullptr;
-  uint32_t *nstart = nullptr; // per-body node counts, scanned in place to pre-order bases
+  uint32_t *nstart = nullptr; // per-body exclusive node-count prefix inside its 256-body block (+ sort.bsum block bases = pre-order index)
   SortScratch sort{};
   TreeArrays T{};
   float4 *sbody = nullptr; // bodies in tree order: (x, y, mass f32, mass bits)
@@ -238,18 +238,19 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += 5; // morton, count, emit, link, finish (+ sort and scan, counted there)
+  g_launches += 6; // morton, count, block-base scan, emit, link, finish (+ the sort, counted there)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st, c->meta);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
   const uint32_t gb = cdiv(n, 256);
-  if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
-  else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart);
-  exclusive_scan_u32(c->nstart, c->nstart, &c->meta->n_in, n, c->sort.bsum, &c->meta->n_nodes, st);
-  if (c->quad) tree_emit_quad_kernel<<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
-  else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, c->T);
+  uint32_t *bbase = c->sort.bsum; // per-256-body block: node count, then (scan_bsum_kernel) the block's first node index
+  if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
+  else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
+  scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes);
+  if (c->quad) tree_emit_quad_kernel<<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
+  else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
   if (c->quad) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   else tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
@@ -545,7 +546,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->sort.ghist, (size_t)4096));
   NB_TRY(dmalloc(&c->sort.tickets, (size_t)16));
   NB_TRY(dmalloc(&c->sort.status, c->sort.status_words));
-  NB_TRY(dmalloc(&c->sort.bsum, na / kScanTile + 16));
+  NB_TRY(dmalloc(&c->sort.bsum, na / 256 + 16)); // block totals of tree_count_kernel (256 bodies) / of the flag scan
   const size_t ncap = 2 * na + 65536;
   c->T.capacity = (uint32_t)std::min<size_t>(ncap, 0xfffffff0u);
   NB_TRY(dmalloc(&c->T.box, (size_t)c->T.capacity));

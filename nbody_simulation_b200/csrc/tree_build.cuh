@@ -75,11 +75,20 @@ __device__ __forceinline__ uint32_t find_end(const unsigned long long *__restric
 // shared memory, forms the window prefixes once and every body takes the maximum over its cap+1 windows.
 constexpr int kCapMax = 64; // nb_create bounds leaf_cap by this
 
+// Pre-order index of the first node body i starts: the count kernel leaves the exclusive prefix inside each
+// 256-body block in nstart[] and the block totals in btotal[], which one scan_bsum_kernel launch turns into block
+// bases (and meta->n_nodes); no separate reduce / apply passes over the bodies.
+__device__ __forceinline__ uint32_t node_base(const uint32_t *__restrict__ nstart, const uint32_t *__restrict__ bbase,
+                                              uint32_t i) {
+  return nstart[i] + bbase[i >> 8];
+}
+
 // Pass 1: L(i) and the number of nodes body i starts.
 template <int BPL, bool COMPRESS>
 __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
                                                          int cap, uint8_t *__restrict__ leafdepth,
-                                                         uint32_t *__restrict__ nstart) {
+                                                         uint32_t *__restrict__ nstart,
+                                                         uint32_t *__restrict__ btotal) {
   const uint32_t n_in = meta->n_in;
   const uint32_t i0 = blockIdx.x * blockDim.x;
   const uint32_t i = i0 + threadIdx.x;
@@ -132,7 +141,12 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
         }
       }
     }
-    nstart[i] = cnt;
+  }
+  { // first half of the device-wide scan: exclusive prefix inside the block, block total for scan_bsum_kernel
+    uint32_t tot;
+    const uint32_t ex = block_exclusive_scan<256>(cnt, tot);
+    if (i < n_in) nstart[i] = ex;
+    if (threadIdx.x == 0) btotal[blockIdx.x] = tot;
   }
   // block-aggregated statistics
   uint32_t leaves = __syncthreads_count(isleaf);
@@ -149,11 +163,12 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
   }
 }
 
-// Pass 2 (after the scan of nstart into base, total in meta->n_nodes): write the nodes.
+// Pass 2 (after scan_bsum_kernel: block bases in bbase, total in meta->n_nodes): write the nodes.
 template <int BPL, bool COMPRESS>
 __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
                                                         const uint8_t *__restrict__ leafdepth,
-                                                        const uint32_t *__restrict__ base, TreeArrays T) {
+                                                        const uint32_t *__restrict__ nstart,
+                                                        const uint32_t *__restrict__ bbase, TreeArrays T) {
   const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
   if (n_nodes > T.capacity) {
     if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
@@ -165,7 +180,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
   const int L = leafdepth[i];
   const int c = (i > 0) ? cpl<BPL>(skeys[i - 1], ki) : -1;
   if (c >= L) return;
-  uint32_t idx = base[i];
+  uint32_t idx = node_base(nstart, bbase, i);
   if (!COMPRESS) {
     // walk the reference's f32 midline chain (quad_tree.rs:172-194) down to depth L
     float ox = meta->x0, oy = meta->y0, hh = meta->h;
@@ -174,7 +189,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
       if (l > c) {
         e = find_end<BPL>(skeys, i, ki, l, e);
         const bool leaf = (l == L);
-        const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
+        const uint32_t skip = (e < n_in) ? node_base(nstart, bbase, e) : n_nodes;
         T.depth[idx] = l;
         T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
         T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
@@ -195,7 +210,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
     for (;;) {
       const int delta = cpl<BPL>(ki, skeys[e - 1]);
       const bool leaf = (delta >= L);
-      const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
+      const uint32_t skip = (e < n_in) ? node_base(nstart, bbase, e) : n_nodes;
       T.depth[idx] = delta;
       T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
       ++idx;
@@ -214,7 +229,8 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
 constexpr int kEmitBodies = 1024;
 __global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
                                                              const uint8_t *__restrict__ leafdepth,
-                                                             const uint32_t *__restrict__ base, TreeArrays T) {
+                                                             const uint32_t *__restrict__ nstart,
+                                                             const uint32_t *__restrict__ bbase, TreeArrays T) {
   const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
   if (n_nodes > T.capacity) {
     if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
@@ -287,8 +303,8 @@ __global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long
       oy = (dg & 2u) ? my : oy;
     }
     const uint32_t e = find_end<2>(skeys, i, ki, level, n_in);
-    const uint32_t skip = (e < n_in) ? base[e] : n_nodes;
-    const uint32_t idx = base[i] + off;
+    const uint32_t skip = (e < n_in) ? node_base(nstart, bbase, e) : n_nodes;
+    const uint32_t idx = node_base(nstart, bbase, i) + off;
     T.depth[idx] = level;
     T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
     T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
