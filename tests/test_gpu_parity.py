@@ -54,6 +54,21 @@ def test_tree_bitexact(tree, okind, sc, n):
     w.close()
 
 
+@pytest.mark.parametrize("tree,okind,cap", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD, 1), (nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD, 3),
+                                            (nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD, 33), (nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD, 64),
+                                            (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH, 1), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH, 7),
+                                            (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH, 40)])
+def test_tree_bitexact_other_leaf_caps(tree, okind, cap):
+    # leaf_cap is a runtime field (MAX_CAPACITY quad_tree.rs:54 / TARGET_POINTS bvh_tree.rs:37 are consts in the
+    # reference): the window of the count kernel, the register / warp / generic leaf fix-up paths all depend on it
+    p = scene("galaxy", 70_001, seed=5)
+    w = nb.World(len(p), tree=tree, leaf_cap=cap)
+    w.set_particles(p)
+    w.build_tree()
+    assert_tree_equal(w.tree(), ob.Tree(okind, p["x"], p["y"], p["weight"], cap=cap).export(), f"cap {cap}/{tree}")
+    w.close()  # (the literal insert-built oracle tree uses the reference's constant capacity: compared at cap 8 above)
+
+
 @pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
 @pytest.mark.parametrize("theta", [0.5, 50.0])
 def test_accel_exact_is_bit_identical(tree, okind, theta):
