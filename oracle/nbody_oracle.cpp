@@ -1140,6 +1140,50 @@ int orc_group_walk_stats(void *h, float theta, int G, double *out) {
   return 0;
 }
 
+// Histogram of leaf-loop trips by the number of unmasked bodies in the group at the leaf visit:
+// hist[a] = sum over leaf visits with a unmasked bodies of the leaf's body count (a = 0..G).  Kernel-design aid.
+int orc_group_walk_leaf_hist(void *h, float theta, int G, double *hist) {
+  OrcTree *T = (OrcTree *)h;
+  const FlatTree &t = T->flat;
+  const uint32_t nn = (uint32_t)t.depth.size();
+  const size_t n = t.n;
+  std::vector<double> acc(G + 1, 0.0);
+#pragma omp parallel
+  {
+    std::vector<double> a(G + 1, 0.0);
+    std::vector<uint32_t> resume(G);
+#pragma omp for schedule(dynamic, 64)
+    for (long long g0 = 0; g0 < (long long)n; g0 += G) {
+      int gs = (int)std::min<size_t>(G, n - g0);
+      for (int k = 0; k < gs; ++k) resume[k] = 0;
+      uint32_t cur = 0;
+      while (cur < nn) {
+        if (t.leaf[cur]) {
+          int act = 0;
+          for (int k = 0; k < gs; ++k) act += (cur >= resume[k]);
+          a[act] += t.count[cur];
+          cur = cur + 1;
+        } else {
+          bool any_open = false;
+          V2 cog{t.cogx[cur], t.cogy[cur]};
+          for (int k = 0; k < gs; ++k) {
+            if (cur < resume[k]) continue;
+            V2 p{t.sx[g0 + k], t.sy[g0 + k]};
+            bool contains = p.y > t.y0[cur] && p.x > t.x0[cur] && p.x < t.x1[cur] && p.y < t.y1[cur];
+            if (!contains && t.s2[cur] < dist2(p, cog) * theta * theta) resume[k] = t.skip[cur];
+            else any_open = true;
+          }
+          cur = any_open ? cur + 1 : t.skip[cur];
+        }
+      }
+    }
+#pragma omp critical
+    for (int k = 0; k <= G; ++k) acc[k] += a[k];
+  }
+  for (int k = 0; k <= G; ++k) hist[k] = acc[k];
+  return 0;
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
