@@ -238,7 +238,7 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += 6; // morton, count, block-base scan, emit, link, finish (+ the sort, counted there)
+  g_launches += c->quad ? 5 : 6; // morton, count, block-base scan, emit, (link,) finish (+ the sort, counted there)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st, c->meta);
   c->sorted_in = which;
@@ -249,11 +249,17 @@ int enqueue_build(nb_ctx *c) {
   if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
   scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes);
-  if (c->quad) tree_emit_quad_kernel<<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
+  // Parent / children / twig links: from the parents' side, either inside the emit kernel (extra searches on the
+  // ~30 % of lanes that hold internal nodes) or by tree_link_kernel (chases skip links).  Measured build phase,
+  // link kernel vs emit: 1M 0.298 / 0.313 ms, 2M 0.515 / 0.517, 4M 0.813 / 0.807, 8M 1.586 / 1.467 — once the node
+  // arrays outgrow L2 the separate pass pays for re-reading them.
+  const bool emit_links = n >= 4000000u;
+  if (c->quad && emit_links) tree_emit_quad_kernel<true><<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
+  else if (c->quad) tree_emit_quad_kernel<false><<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
-  if (c->quad) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
-  else tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
+  if (!c->quad) tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
+  else if (!emit_links) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
   // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
   const uint32_t fin_blocks = std::max((uint32_t)kSMs * 16u, cdiv(n / 2u, 128u)); // measured: 0.38 -> 0.36 ms build at 1M, 2.32 -> 1.91 at 8M

@@ -227,6 +227,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
 // walks the reference's f32 midline chain (quad_tree.rs:172-194) from the root to its own level — the same
 // operations in the same order as the per-body walk, so the boxes are bit-identical.
 constexpr int kEmitBodies = 1024;
+template <bool LINK>
 __global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
                                                              const uint8_t *__restrict__ leafdepth,
                                                              const uint32_t *__restrict__ nstart,
@@ -305,8 +306,36 @@ __global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long
     const uint32_t e = find_end<2>(skeys, i, ki, level, n_in);
     const uint32_t skip = (e < n_in) ? node_base(nstart, bbase, e) : n_nodes;
     const uint32_t idx = node_base(nstart, bbase, i) + off;
+    // An internal node also links its children: child q starts at the first body whose depth-(level+1) prefix
+    // differs from child q-1's, and since that body's predecessor lies in a sibling cell the first node it starts
+    // IS the child.  The parent writes the children's parent field, its own children table and its twig bit
+    // (all children leaves), so no separate pass chases skip links.
+    bool twig = false;
+    if (LINK && !leaf) {
+      uint32_t kid[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      uint32_t b = i;
+      unsigned long long kb = ki;
+      bool all_leaf = true;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (b < e) {
+          const uint32_t cidx = (q == 0) ? idx + 1 : node_base(nstart, bbase, b);
+          kid[q] = cidx;
+          all_leaf = all_leaf && ((int)leafdepth[b] == level + 1);
+          reinterpret_cast<uint32_t *>(&T.link(cidx))[3] = idx;
+          b = find_end<2>(skeys, b, kb, level + 1, e);
+          if (b < e) kb = skeys[b];
+        }
+      }
+      T.kids[idx] = make_uint4(kid[0], kid[1], kid[2], kid[3]);
+      twig = all_leaf;
+    }
     T.depth[idx] = level;
-    T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
+    uint32_t *lk = reinterpret_cast<uint32_t *>(&T.link(idx)); // [3] (parent) belongs to the parent's thread
+    *reinterpret_cast<uint2 *>(lk) = make_uint2(skip, i);
+    lk[2] = (e - i) | (leaf ? kLeafBit : 0u) | (twig ? kTwigBit : 0u);
+    if (!LINK || idx == 0) lk[3] = 0xffffffffu; // !LINK: tree_link_kernel fills it in (and resets arrive[])
+    if (LINK) T.arrive[idx] = 0;
     T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
     T.cm(idx) = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
   }
