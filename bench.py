@@ -304,7 +304,8 @@ def main():
             "wall_ms_per_step_incl_flush": wall / args.steps * 1e3,
             "clocks": clocks,
             "gpu_launches": int(c.launches),
-            "roofline": {"bound": "fp32", "kernel": "traverse_kernel", "achieved": trav_tflops,
+            "roofline": {"bound": "fp32", "kernel": "traverse_fast_kernel" if args.force == "fast" else "traverse_kernel",
+                         "achieved": trav_tflops,
                          "peak": fp32_peak, "unit": "TFLOP/s", "frac": trav_tflops / fp32_peak, "traffic": traffic,
                          "peak_source": ("FFMA microbenchmark (nb_measure_fp32 kind 0) measured in this run; "
                                          f"nominal 148 SM x 128 lanes x 2 flop x {fmax:.0f} MHz = {fp32_nominal:.1f}; "
