@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--tree", default="quad", choices=["quad", "lbvh", "bvhref"])
     ap.add_argument("--theta", type=float, default=0.5)
     ap.add_argument("--force", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU slice exchange: NVLink stores from the integrate kernel, or ncclAllGather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
@@ -217,6 +219,13 @@ def main():
             uid.copy_(torch.from_numpy(nb.World.comm_unique_id()))
         dist.broadcast(uid, 0)
         w.comm_init(rank, world, uid.cpu().numpy())
+        if args.exchange == "peer" and world <= 8:
+            # fused integrate + exchange: every rank maps the peers' body arrays (CUDA IPC) and the integrate kernel
+            # stores its slice into all of them over NVLink; the handle blocks travel through torch.distributed
+            mine = torch.from_numpy(w.comm_peer_export()).cuda()
+            blocks = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(blocks, mine)
+            w.comm_peer_import(torch.stack(blocks).cpu().numpy())
     w.set_particles(parts)
 
     # ---- interaction count of the timed steps: an identical (deterministic) replay with the diagnostic
@@ -293,7 +302,7 @@ def main():
             "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args, n_total), "n_bodies": n_total, "theta": args.theta,
-                       "tree": args.tree, "force_mode": args.force, "parallelism": f"morton-range x{world}",
+                       "tree": args.tree, "force_mode": args.force, "parallelism": f"morton-range x{world}" + (f", exchange={args.exchange}" if world > 1 else ""),
                        "l2": "not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps",
                        "interaction_count": "from an identical replay of the timed steps with counters on"},
             "steps_per_s": args.steps / dev_s,

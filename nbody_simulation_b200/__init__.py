@@ -259,6 +259,17 @@ class World:
         uid = np.ascontiguousarray(uid, dtype=np.uint8)
         self._ck(self._L.nb_comm_init(self._ctx, rank, n_ranks, uid.ctypes.data))
 
+    def comm_peer_export(self):
+        """This rank's block of CUDA IPC handles for the peer-store exchange (all-gather them in rank order)."""
+        buf = np.zeros(_lib.NB_PEER_BLOCK_BYTES, np.uint8)
+        self._ck(self._L.nb_comm_peer_export(self._ctx, buf.ctypes.data))
+        return buf
+
+    def comm_peer_import(self, blocks):
+        """blocks: the n_ranks export blocks in rank order; switches the exchange from ncclAllGather to NVLink stores."""
+        blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+        self._ck(self._L.nb_comm_peer_import(self._ctx, blocks.ctypes.data))
+
     def owned_range(self):
         f, c = C.c_uint64(), C.c_uint64()
         self._ck(self._L.nb_comm_owned_range(self._ctx, C.byref(f), C.byref(c)))

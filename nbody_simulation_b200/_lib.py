@@ -16,6 +16,7 @@ NB_TREE_QUAD, NB_TREE_LBVH, NB_TREE_BVH_REF = 0, 1, 2
 NB_FORCE_EXACT, NB_FORCE_FAST = 0, 1
 NB_SCENE_DEFAULT, NB_SCENE_UNIFORM_DISC, NB_SCENE_PLUMMER, NB_SCENE_TWO_GALAXY = range(4)
 NB_UNIQUE_ID_BYTES = 128
+NB_PEER_BLOCK_BYTES = 640
 
 # struct nb_particle (24 B) == reference `Particle` (src/main.rs:193-198)
 PARTICLE_DTYPE = np.dtype(
@@ -145,6 +146,8 @@ def load(path=LIB_PATH):
         "nb_comm_unique_id": (C.c_int, [vp]),
         "nb_comm_init": (C.c_int, [vp, C.c_int, C.c_int, vp]),
         "nb_comm_owned_range": (C.c_int, [vp, P(C.c_uint64), P(C.c_uint64)]),
+        "nb_comm_peer_export": (C.c_int, [vp, vp]),
+        "nb_comm_peer_import": (C.c_int, [vp, vp]),
         "nb_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, P(C.c_uint64), P(C.c_uint64)]),
         "nb_scene_generate": (C.c_size_t, [C.c_int32, C.c_uint64, C.c_size_t, vp, C.c_size_t]),
         "nb_scene_generate_device": (C.c_int, [vp, C.c_int32, C.c_uint64, C.c_size_t]),

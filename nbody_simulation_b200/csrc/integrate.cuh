@@ -73,6 +73,64 @@ __global__ void __launch_bounds__(256) permute_mid_kernel(const uint32_t *__rest
   out.id[j] = in.id[s];
 }
 
+// ---- multi-GPU peer exchange (NVLink stores instead of ncclAllGather) -------------------------------------
+// integrate_push_kernel is integrate_resort_kernel whose position / velocity stores go to EVERY rank's copy of
+// the output arrays (CUDA IPC mappings of the peers' buffers; index r == own rank is the local array), so the
+// slice travels over NVLink while the kernel is still integrating.  Ranks then hand-shake through epoch flags:
+// peer_signal_kernel runs after the push in stream order (its stores are complete at the kernel boundary),
+// fences at system scope and writes this rank's epoch into every peer's flag word; peer_wait_kernel spins until
+// every rank's flag reached the epoch.  A peer may start overwriting a buffer only after that hand-shake, i.e.
+// after every rank finished reading it.
+constexpr int kMaxPeers = 8;
+struct PeerOut { float *x[kMaxPeers], *y[kMaxPeers], *vx[kMaxPeers], *vy[kMaxPeers]; };
+struct PeerFlags { uint32_t *flags[kMaxPeers]; }; // flags[r] = rank r's flag array, indexed by the writer's rank
+
+__global__ void __launch_bounds__(256) integrate_push_kernel(const uint32_t *__restrict__ order,
+                                                             const float2 *__restrict__ sacc, BodyArrays in,
+                                                             BodyArrays out, PeerOut po, int n_ranks, uint32_t jfirst,
+                                                             uint32_t jcount, float dt) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= jcount) return;
+  const uint32_t j = jfirst + k;
+  const uint32_t s = order[j];
+  const float2 a = sacc[j];
+  const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
+  const float vy = __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
+  const float x = __fadd_rn(in.x[s], __fmul_rn(vx, dt));
+  const float y = __fadd_rn(in.y[s], __fmul_rn(vy, dt));
+  for (int r = 0; r < n_ranks; ++r) {
+    po.vx[r][j] = vx;
+    po.vy[r][j] = vy;
+    po.x[r][j] = x;
+    po.y[r][j] = y;
+  }
+  out.m[j] = in.m[s];
+  out.id[j] = in.id[s];
+}
+
+__global__ void peer_signal_kernel(PeerFlags pf, int n_ranks, int rank, uint32_t epoch) {
+  if ((int)threadIdx.x < n_ranks) {
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t *>(pf.flags[threadIdx.x] + rank) = epoch;
+  }
+}
+
+__global__ void peer_wait_kernel(const uint32_t *my_flags, int n_ranks, uint32_t epoch, Meta *meta) {
+  if ((int)threadIdx.x < n_ranks) {
+    const volatile uint32_t *f = my_flags + threadIdx.x;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while ((int32_t)(*f - epoch) < 0) {
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 10000000000ull) { // 10 s: a peer is gone; do not hang the device
+        meta->error |= 4u;
+        break;
+      }
+    }
+    __threadfence_system();
+  }
+}
+
 __global__ void __launch_bounds__(256) aos_to_soa_kernel(const float *__restrict__ aos /*6 words per body*/,
                                                          BodyArrays b, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

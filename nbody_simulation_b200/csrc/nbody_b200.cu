@@ -118,6 +118,13 @@ struct nb_ctx {
   // multi-GPU
   int rank = 0, n_ranks = 1;
   ncclComm_t comm = nullptr;
+  // peer-store exchange (nb_comm_peer_import): IPC mappings of every rank's x/y/vx/vy (both ping-pong parities)
+  bool peer = false;
+  PeerOut peer_out[2]{};          // by output parity
+  PeerFlags peer_flags_of{};      // every rank's flag array
+  uint32_t *peer_flags = nullptr; // this rank's flag array: [r] = epoch of rank r's last completed push
+  uint32_t peer_epoch = 0;
+  std::vector<void *> peer_mapped; // pointers to close in nb_destroy
 
   std::string err;
 };
@@ -300,7 +307,8 @@ int nccl_fail(nb_ctx *c, ncclResult_t r, const char *what) {
   return fail(c, NB_ERR_NCCL, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
 }
 
-// integrate (main.rs:419-423) fused with the physical re-order; multi-GPU: all-gather slices.
+// integrate (main.rs:419-423) fused with the physical re-order; multi-GPU: the slices are pushed to the peers
+// by the integrate kernel itself (nb_comm_peer_import) or all-gathered by NCCL afterwards.
 int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   const uint32_t n = c->n;
   if (n == 0) return NB_OK;
@@ -314,9 +322,20 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
     invert_order_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, n, pos_of_slot);
     integrate_resort_bug_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, pos_of_slot, c->sacc, in, out, n, dt);
     g_launches += 1;
-  } else if (count)
+  } else if (count && !(c->n_ranks > 1 && c->peer))
     integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt);
-  if (c->n_ranks > 1) {
+  if (c->n_ranks > 1 && c->peer) {
+    // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here
+    if (count)
+      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, c->peer_out[c->cur ^ 1],
+                                                                    c->n_ranks, first, count, dt);
+    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
+    if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
+    ++c->peer_epoch;
+    g_launches += 2;
+    peer_signal_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags_of, c->n_ranks, c->rank, c->peer_epoch);
+    peer_wait_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags, c->n_ranks, c->peer_epoch, c->meta);
+  } else if (c->n_ranks > 1) {
     permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
     const size_t per = cdiv(n, (uint32_t)c->n_ranks);
@@ -340,6 +359,7 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
 int sync_and_check(nb_ctx *c) {
   NB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->meta, sizeof(Meta), cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->h_meta->error & 4u) return fail(c, NB_ERR_NCCL, "peer exchange timed out: a rank did not signal its push within 10 s");
   if (c->h_meta->error & 1u) {
     return fail(c, NB_ERR_OVERFLOW,
                 "node pool too small: " + std::to_string(c->h_meta->n_nodes) + " nodes > capacity " +
@@ -476,6 +496,8 @@ void nb_destroy(nb_ctx *c) {
   cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.ghist); cudaFree(c->sort.tickets); cudaFree(c->sort.status); cudaFree(c->sort.bsum);
   cudaFree(c->T.box); cudaFree(c->T.node); cudaFree(c->T.mass); cudaFree(c->T.depth);
   cudaFree(c->T.bmax); cudaFree(c->T.arrive); cudaFree(c->T.kids);
+  for (void *p : c->peer_mapped) cudaIpcCloseMemHandle(p);
+  cudaFree(c->peer_flags);
   cudaFree(c->sbody); cudaFree(c->sacc); cudaFree(c->bounds_partial); cudaFree(c->meta); cudaFree(c->aos);
   cudaFree(c->flush_buf);
   if (c->h_meta) cudaFreeHost(c->h_meta);
@@ -1041,6 +1063,65 @@ int nb_comm_init(nb_ctx *c, int rank, int n_ranks, const uint8_t id[NB_UNIQUE_ID
   if (r != ncclSuccess) return nccl_fail(c, r, "ncclCommInitRank");
   c->rank = rank;
   c->n_ranks = n_ranks;
+  return NB_OK;
+}
+
+// Block layout: 8 x cudaIpcMemHandle_t for body[parity].{x,y,vx,vy}, 1 for the flag array, u64 array capacity.
+int nb_comm_peer_export(nb_ctx *c, uint8_t block[NB_PEER_BLOCK_BYTES]) {
+  if (!c || !block) return NB_ERR_INVALID;
+  static_assert(9 * sizeof(cudaIpcMemHandle_t) + 8 <= NB_PEER_BLOCK_BYTES, "peer block size");
+  if (c->n_ranks < 2 || c->n_ranks > kMaxPeers) return fail(c, NB_ERR_INVALID, "peer exchange needs 2..8 ranks (nb_comm_init first)");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  if (!c->peer_flags) {
+    NB_CUDA(c, cudaMalloc(&c->peer_flags, kMaxPeers * sizeof(uint32_t)));
+    NB_CUDA(c, cudaMemset(c->peer_flags, 0, kMaxPeers * sizeof(uint32_t)));
+  }
+  std::memset(block, 0, NB_PEER_BLOCK_BYTES);
+  cudaIpcMemHandle_t *h = reinterpret_cast<cudaIpcMemHandle_t *>(block);
+  for (int p = 0; p < 2; ++p) {
+    float *arrs[4] = {c->body[p].x, c->body[p].y, c->body[p].vx, c->body[p].vy};
+    for (int a = 0; a < 4; ++a) NB_CUDA(c, cudaIpcGetMemHandle(&h[4 * p + a], arrs[a]));
+  }
+  NB_CUDA(c, cudaIpcGetMemHandle(&h[8], c->peer_flags));
+  const uint64_t cap = c->n_alloc;
+  std::memcpy(block + 9 * sizeof(cudaIpcMemHandle_t), &cap, 8);
+  return NB_OK;
+}
+
+int nb_comm_peer_import(nb_ctx *c, const uint8_t *blocks) {
+  if (!c || !blocks) return NB_ERR_INVALID;
+  if (c->n_ranks < 2 || c->n_ranks > kMaxPeers || !c->peer_flags)
+    return fail(c, NB_ERR_INVALID, "nb_comm_peer_import: call nb_comm_init and nb_comm_peer_export first");
+  if (c->peer) return fail(c, NB_ERR_INVALID, "nb_comm_peer_import: already imported");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  for (int r = 0; r < c->n_ranks; ++r) {
+    const uint8_t *blk = blocks + (size_t)r * NB_PEER_BLOCK_BYTES;
+    const cudaIpcMemHandle_t *h = reinterpret_cast<const cudaIpcMemHandle_t *>(blk);
+    uint64_t cap = 0;
+    std::memcpy(&cap, blk + 9 * sizeof(cudaIpcMemHandle_t), 8);
+    if (cap != c->n_alloc) return fail(c, NB_ERR_INVALID, "nb_comm_peer_import: ranks were created with different n_max");
+    void *ptr[9];
+    for (int k = 0; k < 9; ++k) {
+      if (r == c->rank) {
+        float *own[8] = {c->body[0].x, c->body[0].y, c->body[0].vx, c->body[0].vy,
+                         c->body[1].x, c->body[1].y, c->body[1].vx, c->body[1].vy};
+        ptr[k] = k < 8 ? (void *)own[k] : (void *)c->peer_flags;
+      } else {
+        cudaIpcMemHandle_t hh;
+        std::memcpy(&hh, &h[k], sizeof(hh));
+        NB_CUDA(c, cudaIpcOpenMemHandle(&ptr[k], hh, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_mapped.push_back(ptr[k]);
+      }
+    }
+    for (int p = 0; p < 2; ++p) {
+      c->peer_out[p].x[r] = (float *)ptr[4 * p + 0];
+      c->peer_out[p].y[r] = (float *)ptr[4 * p + 1];
+      c->peer_out[p].vx[r] = (float *)ptr[4 * p + 2];
+      c->peer_out[p].vy[r] = (float *)ptr[4 * p + 3];
+    }
+    c->peer_flags_of.flags[r] = (uint32_t *)ptr[8];
+  }
+  c->peer = true;
   return NB_OK;
 }
 

@@ -22,8 +22,9 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ok = True
-    for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH, nb.NB_TREE_BVH_REF):
-        for n in (100_003, 7):
+    for tree, n, peer in [(t, n, p) for t in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH, nb.NB_TREE_BVH_REF)
+                          for n in (100_003, 7) for p in (False, True)]:
+        if True:
             p = nb.generate_scene(nb.NB_SCENE_TWO_GALAXY, 3, n)
             steps = 5
             w = nb.World(len(p), theta=0.6, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_EXACT, device=local)
@@ -32,6 +33,11 @@ def main():
                 uid.copy_(torch.from_numpy(nb.World.comm_unique_id()))
             dist.broadcast(uid, 0)
             w.comm_init(rank, world, uid.cpu().numpy())
+            if peer:  # NVLink stores from the integrate kernel instead of ncclAllGather
+                mine = torch.from_numpy(w.comm_peer_export()).cuda()
+                blocks = [torch.empty_like(mine) for _ in range(world)]
+                dist.all_gather(blocks, mine)
+                w.comm_peer_import(torch.stack(blocks).cpu().numpy())
             w.set_particles(p)
             c = nb.Counting()
             w.step(steps, c)
@@ -46,7 +52,7 @@ def main():
             dist.all_reduce(tot)
             counts_ok = int(tot.item()) == rc.interactions
             f, cnt = w.owned_range()
-            print(f"rank {rank}/{world} tree={tree} n={len(p)} owned=[{f},{f + cnt}) bit-identical={same} "
+            print(f"rank {rank}/{world} tree={tree} n={len(p)} exchange={'peer' if peer else 'nccl'} owned=[{f},{f + cnt}) bit-identical={same} "
                   f"interactions sum={int(tot.item())} single={rc.interactions} ok={counts_ok} "
                   f"exchange_ms/step={c.exchange / steps * 1e3:.3f}", flush=True)
             ok = ok and same and counts_ok
