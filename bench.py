@@ -222,10 +222,26 @@ def main():
         if args.exchange == "peer" and world <= 8:
             # fused integrate + exchange: every rank maps the peers' body arrays (CUDA IPC) and the integrate kernel
             # stores its slice into all of them over NVLink; the handle blocks travel through torch.distributed
-            mine = torch.from_numpy(w.comm_peer_export()).cuda()
+            ok = 1.0
+            try:
+                mine = torch.from_numpy(w.comm_peer_export()).cuda()
+            except nb.NbError as e:
+                print(f"[bench] rank {rank}: peer export failed ({e}); falling back to ncclAllGather", file=sys.stderr)
+                mine, ok = torch.zeros(nb._lib.NB_PEER_BLOCK_BYTES, dtype=torch.uint8, device="cuda"), 0.0
             blocks = [torch.empty_like(mine) for _ in range(world)]
             dist.all_gather(blocks, mine)
-            w.comm_peer_import(torch.stack(blocks).cpu().numpy())
+            if ok:
+                try:
+                    w.comm_peer_import(torch.stack(blocks).cpu().numpy())
+                except nb.NbError as e:
+                    print(f"[bench] rank {rank}: peer import failed ({e}); falling back to ncclAllGather", file=sys.stderr)
+                    ok = 0.0
+            all_ok = torch.tensor([ok], device="cuda")
+            dist.all_reduce(all_ok, op=dist.ReduceOp.MIN)  # one exchange for everybody
+            if all_ok.item() != 1.0:
+                if ok:
+                    w.comm_peer_enable(False)
+                args.exchange = "nccl"
     w.set_particles(parts)
 
     # ---- interaction count of the timed steps: an identical (deterministic) replay with the diagnostic

@@ -270,6 +270,9 @@ class World:
         blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
         self._ck(self._L.nb_comm_peer_import(self._ctx, blocks.ctypes.data))
 
+    def comm_peer_enable(self, on):
+        self._ck(self._L.nb_comm_peer_enable(self._ctx, 1 if on else 0))
+
     def owned_range(self):
         f, c = C.c_uint64(), C.c_uint64()
         self._ck(self._L.nb_comm_owned_range(self._ctx, C.byref(f), C.byref(c)))

@@ -148,6 +148,7 @@ def load(path=LIB_PATH):
         "nb_comm_owned_range": (C.c_int, [vp, P(C.c_uint64), P(C.c_uint64)]),
         "nb_comm_peer_export": (C.c_int, [vp, vp]),
         "nb_comm_peer_import": (C.c_int, [vp, vp]),
+        "nb_comm_peer_enable": (C.c_int, [vp, C.c_int]),
         "nb_shard_range": (None, [C.c_uint64, C.c_int, C.c_int, P(C.c_uint64), P(C.c_uint64)]),
         "nb_scene_generate": (C.c_size_t, [C.c_int32, C.c_uint64, C.c_size_t, vp, C.c_size_t]),
         "nb_scene_generate_device": (C.c_int, [vp, C.c_int32, C.c_uint64, C.c_size_t]),

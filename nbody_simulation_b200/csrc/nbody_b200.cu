@@ -1125,6 +1125,14 @@ int nb_comm_peer_import(nb_ctx *c, const uint8_t *blocks) {
   return NB_OK;
 }
 
+int nb_comm_peer_enable(nb_ctx *c, int on) {
+  if (!c) return NB_ERR_INVALID;
+  if (on && c->peer_flags_of.flags[c->n_ranks > 0 ? c->n_ranks - 1 : 0] == nullptr)
+    return fail(c, NB_ERR_INVALID, "nb_comm_peer_enable: no imported peer mappings");
+  c->peer = on != 0;
+  return NB_OK;
+}
+
 void nb_shard_range(uint64_t n, int rank, int n_ranks, uint64_t *first, uint64_t *count) {
   if (n_ranks <= 1) {
     *first = 0;
