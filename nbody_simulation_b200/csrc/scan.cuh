@@ -1,4 +1,6 @@
-// scan.cuh — device-wide exclusive prefix sum (u32), three launches, no host sync.
+// scan.cuh — building blocks of the device-wide exclusive prefix sums (u32): warp / block scans and the
+// single-block scan of per-block totals.  The per-element passes live with their producers (tree_count_kernel
+// in tree_build.cuh, the flag scan in bvh_ref.cuh).
 #pragma once
 #include "common.cuh"
 
@@ -40,29 +42,6 @@ template <int NT> __device__ __forceinline__ uint32_t block_exclusive_scan(uint3
   return r;
 }
 
-// n is read from *n_ptr when n_ptr != nullptr (device-resident sizes), else n_host.
-__device__ __forceinline__ uint32_t scan_n(const uint32_t *n_ptr, uint32_t n_host) {
-  return n_ptr ? *n_ptr : n_host;
-}
-
-__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t *__restrict__ in,
-                                                                   const uint32_t *n_ptr, uint32_t n_host,
-                                                                   uint32_t *__restrict__ bsum) {
-  const uint32_t n = scan_n(n_ptr, n_host);
-  const uint32_t base = blockIdx.x * kScanTile;
-  uint32_t s = 0;
-  if (base < n) {
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k) {
-      uint32_t i = base + k * kScanThreads + threadIdx.x;
-      if (i < n) s += in[i];
-    }
-  }
-  uint32_t tot;
-  block_exclusive_scan<kScanThreads>(s, tot);
-  if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
-}
-
 // Single block: exclusive scan of the block sums in place; total -> *total_out.
 __global__ void __launch_bounds__(1024) scan_bsum_kernel(uint32_t *__restrict__ bsum, uint32_t nb,
                                                          uint32_t *total_out) {
@@ -81,42 +60,6 @@ __global__ void __launch_bounds__(1024) scan_bsum_kernel(uint32_t *__restrict__ 
     __syncthreads();
   }
   if (threadIdx.x == 0 && total_out) *total_out = carry_s;
-}
-
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t *__restrict__ in,
-                                                                  uint32_t *__restrict__ out, const uint32_t *n_ptr,
-                                                                  uint32_t n_host, const uint32_t *__restrict__ bsum) {
-  const uint32_t n = scan_n(n_ptr, n_host);
-  const uint32_t base = blockIdx.x * kScanTile;
-  if (base >= n) return;
-  // blocked arrangement: thread t owns items [t*8, t*8+8) of the tile
-  uint32_t v[kScanItems];
-  uint32_t s = 0;
-  const uint32_t i0 = base + threadIdx.x * kScanItems;
-#pragma unroll
-  for (int k = 0; k < kScanItems; ++k) {
-    v[k] = (i0 + k < n) ? in[i0 + k] : 0;
-    s += v[k];
-  }
-  uint32_t tot;
-  uint32_t ex = block_exclusive_scan<kScanThreads>(s, tot) + bsum[blockIdx.x];
-#pragma unroll
-  for (int k = 0; k < kScanItems; ++k) {
-    if (i0 + k < n) out[i0 + k] = ex;
-    ex += v[k];
-  }
-}
-
-// Host helper: enqueue the three launches.  `n_max` bounds the grid; the live size is
-// *n_ptr (device) or n_max.
-inline void exclusive_scan_u32(const uint32_t *in, uint32_t *out, const uint32_t *n_ptr, uint32_t n_max,
-                               uint32_t *bsum_scratch, uint32_t *total_out, cudaStream_t st) {
-  uint32_t nb = (n_max + kScanTile - 1) / kScanTile;
-  if (nb == 0) nb = 1;
-  g_launches += 3;
-  scan_reduce_kernel<<<nb, kScanThreads, 0, st>>>(in, n_ptr, n_max, bsum_scratch);
-  scan_bsum_kernel<<<1, 1024, 0, st>>>(bsum_scratch, nb, total_out);
-  scan_apply_kernel<<<nb, kScanThreads, 0, st>>>(in, out, n_ptr, n_max, bsum_scratch);
 }
 
 } // namespace nb

@@ -181,30 +181,8 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
   const int c = (i > 0) ? cpl<BPL>(skeys[i - 1], ki) : -1;
   if (c >= L) return;
   uint32_t idx = node_base(nstart, bbase, i);
-  if (!COMPRESS) {
-    // walk the reference's f32 midline chain (quad_tree.rs:172-194) down to depth L
-    float ox = meta->x0, oy = meta->y0, hh = meta->h;
-    uint32_t e = n_in;
-    for (int l = 0; l <= L; ++l) {
-      if (l > c) {
-        e = find_end<BPL>(skeys, i, ki, l, e);
-        const bool leaf = (l == L);
-        const uint32_t skip = (e < n_in) ? node_base(nstart, bbase, e) : n_nodes;
-        T.depth[idx] = l;
-        T.link(idx) = make_uint4(skip, i, (e - i) | (leaf ? kLeafBit : 0u), 0xffffffffu);
-        T.box[idx] = make_float4(ox, oy, __fadd_rn(ox, hh), __fadd_rn(oy, hh));
-        T.cm(idx) = make_float4(0.f, 0.f, 0.f, __fmul_rn(hh, hh));
-        ++idx;
-      }
-      if (l < L) {
-        hh = __fmul_rn(hh, 0.5f);
-        const float mx = __fadd_rn(ox, hh), my = __fadd_rn(oy, hh);
-        const uint32_t dg = (uint32_t)(ki >> (kKeyBits - 2 * (l + 1))) & 3u;
-        ox = (dg & 1u) ? mx : ox;
-        oy = (dg & 2u) ? my : oy;
-      }
-    }
-  } else {
+  static_assert(COMPRESS, "the uncompressed quadtree is emitted by tree_emit_quad_kernel");
+  {
     int d = c + 1;
     uint32_t e = find_end<BPL>(skeys, i, ki, d, n_in);
     for (;;) {
