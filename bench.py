@@ -121,6 +121,8 @@ def cpu_port_steps(parts, args, n_steps, warmup, stride, threads=0):
     from nbody_simulation_b200._lib import NbCounting
 
     kind = ob.KIND_LITERAL_QUAD if args.tree == "quad" else ob.KIND_LITERAL_BVH
+    if threads <= 0:  # all usable host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     ow = ob.OracleWorld(parts)
     for _ in range(warmup):
         ow.update(kind, 0.1, args.theta, sample_stride=stride, threads=threads)
@@ -137,7 +139,7 @@ def cpu_port_steps(parts, args, n_steps, warmup, stride, threads=0):
         "interactions_per_step": est_inter / max(1, n_steps),
         "build_s": c.build_s / max(1, n_steps), "traverse_s": c.traverse_s * stride / max(1, n_steps),
         "integrate_s": c.integrate_s / max(1, n_steps), "wall_s": wall,
-        "cores": ob.lib().orc_num_threads() if threads <= 0 else threads,
+        "cores": threads,
     }
 
 
