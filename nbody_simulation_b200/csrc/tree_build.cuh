@@ -392,7 +392,7 @@ template <bool LBVH> struct LeafAcc {
 // gathers and writes the bodies with all lanes, and lane 0 then folds the leaf IN TREE ORDER from a shared
 // staging row (the f32 sum is order dependent) and climbs alone.
 template <bool LBVH, int MAXK, bool REF = false, bool WARP = false>
-__global__ void __launch_bounds__(128) tree_finish_kernel(Meta *__restrict__ meta, TreeArrays T,
+__global__ void __launch_bounds__(128, 12) tree_finish_kernel(Meta *__restrict__ meta, TreeArrays T,
                                                           uint32_t *__restrict__ order, const float *__restrict__ x,
                                                           const float *__restrict__ y, const uint32_t *__restrict__ m,
                                                           const uint32_t *__restrict__ id,
