@@ -245,7 +245,7 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += c->quad ? 5 : 6; // morton, count, block-base scan, emit, (link,) finish (+ the sort, counted there)
+  g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st, c->meta);
   c->sorted_in = which;
@@ -265,6 +265,7 @@ int enqueue_build(nb_ctx *c) {
   else if (c->quad) tree_emit_quad_kernel<false><<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
+  if (!c->quad || !emit_links) g_launches += 1;
   if (!c->quad) tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   else if (!emit_links) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
