@@ -170,13 +170,24 @@ __global__ void __launch_bounds__(kSortThreads) sort_onesweep_kernel(
     const int d = threadIdx.x + q * kSortThreads;
     uint32_t prefix = 0;
     if (tile > 0) {
+      // look back kLookBatch predecessors per round trip: the loads are independent, only the walk over their
+      // values is ordered (tile 0 is always inclusive, so the walk ends at the latest there)
+      constexpr int kLookBatch = 4; // measured at 1M / 8M bodies, build phase: 1: 0.2985 / 1.412 ms, 4: 0.2855 / 1.403, 8: 0.2950 / 1.433
       int t = (int)tile - 1;
-      for (;;) {
-        uint32_t sv;
-        do { sv = status[(size_t)t * RADIX + d]; } while ((sv >> 30) == 0u);
-        prefix += sv & kStatusValue;
-        if ((sv >> 30) == 2u) break;
-        --t;
+      bool done = false;
+      while (!done) {
+        uint32_t sv[kLookBatch];
+#pragma unroll
+        for (int b = 0; b < kLookBatch; ++b) sv[b] = (t - b >= 0) ? status[(size_t)(t - b) * RADIX + d] : 0u;
+#pragma unroll
+        for (int b = 0; b < kLookBatch; ++b) {
+          if (!done) {
+            while ((sv[b] >> 30) == 0u) sv[b] = status[(size_t)(t - b) * RADIX + d];
+            prefix += sv[b] & kStatusValue;
+            done = (sv[b] >> 30) == 2u;
+          }
+        }
+        t -= kLookBatch;
       }
       status[(size_t)tile * RADIX + d] = kFlagInclusive | (prefix + dtot[q]);
     }
