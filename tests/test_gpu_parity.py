@@ -237,6 +237,26 @@ def test_lbvh_auto_domain():
     w.close()
 
 
+@pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
+@pytest.mark.parametrize("domain", [(-20000.0, 12345.678, 123456.7), (1.0e6, 1.0e6, 1.0e5), (16777216.0, 16777216.0, 4096.0)])
+def test_other_fixed_domains(tree, okind, domain):
+    # root squares other than the reference's (0, 0, 100000): keys and trees must equal the oracle's also where the
+    # f32 grid is coarser than the deep cells (offsets of 2^24 with a 4096-wide square) and with bodies outside
+    x0, y0, h = domain
+    rng = np.random.default_rng(11)
+    n = 60_000
+    p = np.zeros(n, dtype=scene("disc", 2).dtype)
+    p["x"] = (x0 + h * rng.uniform(-0.05, 1.05, n)).astype(np.float32)
+    p["y"] = (y0 + h * rng.uniform(-0.05, 1.05, n)).astype(np.float32)
+    p["weight"] = rng.integers(1, 5, n)
+    w = nb.World(n, tree=tree, domain=domain)
+    w.set_particles(p)
+    w.build_tree()
+    o = ob.Tree(okind, p["x"], p["y"], p["weight"], domain=domain).export()
+    assert_tree_equal(w.tree(), o, f"domain {domain}/{tree}")
+    w.close()
+
+
 def test_snapshot_resume_is_bit_identical(tmp_path):
     p = scene("galaxy", 30_000)
     a = nb.World(len(p), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
