@@ -167,5 +167,6 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        _lib = load()
+        # NB_B200_LIB: another build of the same library (A/B runs of a kernel change: scripts/ab_step.py)
+        _lib = load(os.environ.get("NB_B200_LIB") or LIB_PATH)
     return _lib

@@ -292,8 +292,10 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
                                                           c->cfg.theta, first, count)
 #define NB_TRAVERSE_FAST(CNT)                                                                                     \
   traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
-                                                           c->cfg.theta, first, count)
+                                                           theta2, first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
+  const volatile float theta_f = c->cfg.theta;
+  const float theta2 = theta_f * theta_f; // f32 product, rounded once: the bits the device's FMUL would give
   if (ex && c->counting) NB_TRAVERSE(true, true);
   else if (ex) NB_TRAVERSE(true, false);
   else if (c->counting) NB_TRAVERSE_FAST(true);
@@ -862,6 +864,10 @@ int nb_accel_direct(nb_ctx *c, size_t first, size_t count, float *ax, float *ay,
   uint32_t *slot_of = nullptr;
   double *acc = nullptr;
   float *dax = nullptr;
+  struct Scratch { // freed on every return path
+    uint32_t *&a; double *&b; float *&d;
+    ~Scratch() { cudaFree(a); cudaFree(b); cudaFree(d); }
+  } scratch{slot_of, acc, dax};
   NB_CUDA(c, dmalloc(&slot_of, (size_t)n));
   NB_CUDA(c, dmalloc(&acc, 2 * (size_t)nt));
   NB_CUDA(c, dmalloc(&dax, 2 * (size_t)nt));
@@ -892,7 +898,6 @@ int nb_accel_direct(nb_ctx *c, size_t first, size_t count, float *ax, float *ay,
     if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) *seconds = ms * 1e-3;
   }
   c->ev_used = 0;
-  cudaFree(slot_of); cudaFree(acc); cudaFree(dax);
   return NB_OK;
 }
 

@@ -13,7 +13,7 @@
 //  * the opening test and the accepted interaction share diff and |diff|^2: dist2(p, cog)
 //    (main.rs:229-232) squares p - cog, calculate_gravity (main.rs:236,245) squares cog - p — the
 //    same bits — so an accepted node costs 7 more instructions, not 11;
-//  * FAST mode with theta^2 <= 1/2 drops Rectangle::contains: a body strictly inside the box and a
+//  * FAST mode with theta^2 <= 0.49 (kThetaSqNoContains) drops Rectangle::contains: a body strictly inside the box and a
 //    centre of gravity inside the box are at most sqrt(w^2+h^2) <= sqrt(2)*s apart, so
 //    s^2 < d^2*theta^2 cannot hold; the up-sweep flags the (pathological, u32-wrapped-mass) case
 //    of a centre of gravity outside its box and the kernel then keeps the test;
@@ -23,6 +23,13 @@
 #include "tree_build.cuh"
 
 namespace nb {
+
+// Largest theta^2 for which FAST mode may drop Rectangle::contains.  The up-sweep raises meta.cog_outside unless
+// every centre of gravity lies within 1 % of its box (tree_build.cuh), so for a body strictly inside a w x h box
+// |dx| < 1.01 w and |dy| < 1.01 h: d^2 < 1.0201 (w^2 + h^2) <= 2.0402 s^2 with s = max(w, h), and the acceptance
+// s^2 < d^2 theta^2 cannot hold while 2.0402 theta^2 <= 1, i.e. theta^2 <= 0.49015.  0.49 keeps a 3e-4 relative
+// margin over the f32 rounding of d^2 and the product (~3e-7), and covers theta = 0.7 (0.7f^2 = 0.48999998).
+constexpr float kThetaSqNoContains = 0.49f;
 
 // main.rs:235-253 with diff = (dx, dy) and d2 = dx*dx + dy*dy already computed.
 template <bool EXACT>
@@ -73,8 +80,7 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
   const uint32_t n_nodes = meta->n_nodes;
   const float theta2 = theta * theta;
   // Rectangle::contains is needed unless provably implied (see header)
-  // (0.45 rather than 0.5 leaves slack for the 1% excursion the up-sweep tolerates)
-  const bool need_contains = EXACT || !(theta2 <= 0.45f) || meta->cog_outside != 0;
+  const bool need_contains = EXACT || !(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0;
   uint32_t cur = 0;
   while (cur < n_nodes) {
     float4 c;
@@ -181,7 +187,7 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 template <bool COUNT, bool CONTAINS>
 __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
                                                    Meta *meta, const float4 *__restrict__ sbody,
-                                                   float2 *__restrict__ sacc, float theta, uint32_t tfirst,
+                                                   float2 *__restrict__ sacc, const float theta2_in, uint32_t tfirst,
                                                    uint32_t tcount) {
   const unsigned lane = threadIdx.x & 31;
   const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
@@ -194,14 +200,23 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   uint32_t resume = valid ? 0u : 0xffffffffu;
   uint32_t n_inter = 0, n_test = 0;
   const uint32_t n_nodes = meta->n_nodes;
-  const float theta2 = theta * theta;
+  // theta^2 is made to depend on loaded data (n_nodes < 2^31, so the shift adds 0): ptxas then keeps it in a
+  // register; as a plain kernel parameter it is re-read from the constant bank on every visit, and the kernel
+  // is bound by issue slots.
+  const float theta2 = __uint_as_float(__float_as_uint(theta2_in) + (n_nodes >> 31));
+  // The odd first body of a leaf must stay behind a (warp-uniform) branch: ptxas if-converts `if (k & 1)` into 16
+  // predicated issue slots on every even leaf.  `one` is 1 (same n_nodes < 2^31 argument), but not provably so,
+  // which keeps the loop over `k & one` a real loop.
+  const uint32_t one = 1u + ((n_nodes >> 31) << 8);
+  const float2 np = make_float2(-px, -py);
   uint32_t cur = 0;
   while (cur < n_nodes) {
     float4 c;
     uint4 l;
     load_node(node + 2 * (size_t)cur, c, l);
     const bool active = cur >= resume;
-    const float dx = c.x - px, dy = c.y - py;
+    const float2 dn = __fadd2_rn(make_float2(c.x, c.y), np); // one packed FADD2 for both components (same bits as c - p)
+    const float dx = dn.x, dy = dn.y;
     const float d2 = fmaf(dy, dy, dx * dx);
     bool far = c.w < d2 * theta2;
     if (CONTAINS) {
@@ -219,25 +234,30 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
         n_inter += (acc ? 1u : 0u) + (take ? k : 0u);
       }
       if (__any_sync(0xffffffffu, take)) {
-        // warp-uniform trip count; every lane runs the leaf on a copy of its sum and only the takers keep it
+        // warp-uniform trip count; every lane runs the leaf on a copy of its sum and only the takers keep it.
+        // Bodies are summed in index order: an odd first body alone, then pairs.  The loop is kept rolled on
+        // purpose: leaves hold 4-5 bodies on average, and the dispatch code of an unrolled loop with remainder
+        // loops cost more issue slots per visit than it saved.
         const float4 *bp = sbody + l.y;
         float lx = ax, ly = ay; // continue the lane's own running sum: same summation order as the scalar walk
-        uint32_t j = 0;
-#pragma unroll 2
-        for (; j + 1 < k; j += 2) {
-          const float4 b0 = bp[j];
-          const float4 b1 = bp[j + 1];
-          const float dx0 = b0.x - px, dy0 = b0.y - py, dx1 = b1.x - px, dy1 = b1.y - py;
+#pragma unroll 1
+        for (uint32_t o = k & one; o != 0u; --o) { // at most one trip; see `one`
+          const float4 b0 = *bp++;
+          const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), np);
+          const float dx0 = e0.x, dy0 = e0.y;
+          const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
+          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
+        }
+#pragma unroll 1
+        for (uint32_t j = k >> 1; j != 0u; --j, bp += 2) {
+          const float4 b0 = bp[0];
+          const float4 b1 = bp[1];
+          const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), np), e1 = __fadd2_rn(make_float2(b1.x, b1.y), np);
+          const float dx0 = e0.x, dy0 = e0.y, dx1 = e1.x, dy1 = e1.y;
           const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
           const float w1 = b1.z * rcp_approx(fmaf(fabsf(dx1) + fabsf(dy1), fmaxf(fmaf(dy1, dy1, dx1 * dx1), 0.001f), 1e-20f));
           lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
           lx = fmaf(dx1, w1, lx); ly = fmaf(dy1, w1, ly);
-        }
-        if (j < k) {
-          const float4 b0 = bp[j];
-          const float dx0 = b0.x - px, dy0 = b0.y - py;
-          const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
-          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
         }
         ax = take ? lx : ax; // selects, not a branch: the loop body of the walk stays convergent
         ay = take ? ly : ay;
@@ -271,19 +291,20 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   }
 }
 
+// theta2 = theta * theta comes in as a kernel parameter (the host's f32 product has the same bits as the device's):
+// the walk then multiplies by a constant-bank operand, where a register copy was being recomputed on every visit.
 template <bool COUNT>
 __global__ void __launch_bounds__(256) traverse_fast_kernel(const float4 *__restrict__ box,
                                                             const float4 *__restrict__ node, Meta *meta,
                                                             const float4 *__restrict__ sbody,
-                                                            float2 *__restrict__ sacc, float theta, uint32_t tfirst,
+                                                            float2 *__restrict__ sacc, float theta2, uint32_t tfirst,
                                                             uint32_t tcount) {
   if (meta->error) return;
-  // Rectangle::contains is needed unless provably implied (see the header of this file); 0.45 rather than
-  // 0.5 leaves slack for the 1% excursion the up-sweep tolerates before it raises cog_outside
-  if (!(theta * theta <= 0.45f) || meta->cog_outside != 0)
-    traverse_fast_body<COUNT, true>(box, node, meta, sbody, sacc, theta, tfirst, tcount);
+  // Rectangle::contains is needed unless provably implied (kThetaSqNoContains)
+  if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0)
+    traverse_fast_body<COUNT, true>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
   else
-    traverse_fast_body<COUNT, false>(box, node, meta, sbody, sacc, theta, tfirst, tcount);
+    traverse_fast_body<COUNT, false>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
 }
 
 } // namespace nb

@@ -84,11 +84,12 @@ def test_accel_exact_is_bit_identical(tree, okind, theta):
     w.close()
 
 
+# theta 0.5 and 0.7: Rectangle::contains elided (theta^2 <= 0.49, traverse.cuh kThetaSqNoContains); 0.9: kept
+@pytest.mark.parametrize("theta", [0.5, 0.7, 0.9])
 @pytest.mark.parametrize("tree,okind", [(nb.NB_TREE_QUAD, ob.KIND_PIPE_QUAD), (nb.NB_TREE_LBVH, ob.KIND_PIPE_LBVH)])
-def test_accel_fast_within_tolerance(tree, okind):
+def test_accel_fast_within_tolerance(tree, okind, theta):
     # tolerance: normwise ||da||2/||a||2 <= 1e-5 against the oracle on the SAME tree and theta
     p = scene("disc", 200_000)
-    theta = 0.5
     w = nb.World(len(p), theta=theta, tree=tree, force_mode=nb.NB_FORCE_FAST)
     w.set_particles(p)
     c = nb.Counting()
