@@ -39,7 +39,8 @@ class NbConfig(C.Structure):
         ("force_mode", C.c_int32),
         ("device", C.c_int32),
         ("faithful_index_bug", C.c_int32),
-        ("reserved", C.c_int32 * 8),
+        ("full_sort", C.c_int32),
+        ("reserved", C.c_int32 * 7),
     ]
 
 
@@ -69,7 +70,9 @@ class NbTreeInfo(C.Structure):
         ("root_x0", C.c_float),
         ("root_y0", C.c_float),
         ("root_h", C.c_float),
-        ("reserved", C.c_uint32 * 5),
+        ("sort_top_digits", C.c_uint32),
+        ("sort_redone", C.c_uint32),
+        ("reserved", C.c_uint32 * 3),
     ]
 
 

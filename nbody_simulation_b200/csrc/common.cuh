@@ -25,6 +25,7 @@ struct Meta {
   uint32_t overflow_leaves;
   uint32_t error;           // bit 0: node pool too small
   uint32_t cog_outside;     // != 0: some internal node's centre of gravity lies outside its box
+  uint32_t resort;          // != 0: the top-digit sort of this step was too shallow for the tree (radix_sort.cuh)
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)
 };

@@ -109,6 +109,10 @@ struct nb_ctx {
   void *flush_buf = nullptr;
   size_t flush_bytes = 0;
   bool tree_valid = false;
+  bool depth_known = false;    // last_max_depth comes from a completed quadtree build of the current body set
+  uint32_t last_max_depth = 0; // deepest leaf of the last checked build: sizes the next step's top-digit sort
+  uint32_t resorts = 0;        // builds (as seen at the checks) whose top-digit sort had to be redone in full
+  int last_top_passes = 0;     // top digits the last build sorted before checking (0 = full sort)
   bool counting = true; // interaction / opening-test counters in the traversal
   unsigned long long seen_interactions = 0, seen_tests = 0;
 
@@ -247,15 +251,34 @@ int enqueue_build(nb_ctx *c) {
   }
   g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
-  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st, c->meta);
+  // Quadtree: sort only as many top digits as the previous build's depth (+1 level) needs; tree_count_kernel
+  // verifies, and the conditional passes behind it redo the sort in full if the guess was too shallow
+  // (radix_sort.cuh).  Digit p from the top covers 4 quadtree levels (the top digit also holds the outside bit).
+  int top_passes = 0;
+  if (c->quad && c->depth_known && !c->cfg.full_sort) {
+    const int want = ((int)c->last_max_depth + 1 + 3) / 4;
+    top_passes = want < 2 ? 2 : want;
+    if (!sort_can_speculate(make_sort_plan(49), top_passes)) top_passes = 0;
+  }
+  c->last_top_passes = top_passes;
+  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
+                                     c->meta, top_passes);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
   const uint32_t gb = cdiv(n, 256);
   uint32_t *bbase = c->sort.bsum; // per-256-body block: node count, then (scan_bsum_kernel) the block's first node index
-  if (c->quad) tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
+  if (c->quad)
+    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
-  scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes);
+  scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, c->meta);
+  if (top_passes) {
+    const uint32_t *cond = &c->meta->resort;
+    radix_sort_fallback(c->keys[0], c->vals[0], c->keys[1], c->vals[1], which, n, 49, top_passes, c->sort, st, cond);
+    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 0, cond);
+    scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, nullptr, cond);
+    g_launches += 2;
+  }
   // Parent / children / twig links: from the parents' side, either inside the emit kernel (extra searches on the
   // ~30 % of lanes that hold internal nodes) or by tree_link_kernel (chases skip links).  Measured build phase,
   // link kernel vs emit: 1M 0.298 / 0.313 ms, 2M 0.515 / 0.517, 4M 0.813 / 0.807, 8M 1.586 / 1.467 — once the node
@@ -362,6 +385,11 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
 int sync_and_check(nb_ctx *c) {
   NB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->meta, sizeof(Meta), cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->quad && c->n && c->h_meta->n_nodes) { // the mirror describes the last build enqueued
+    c->last_max_depth = c->h_meta->max_depth;
+    c->depth_known = true;
+    if (c->h_meta->resort) ++c->resorts;
+  }
   if (c->h_meta->error & 4u) return fail(c, NB_ERR_NCCL, "peer exchange timed out: a rank did not signal its push within 10 s");
   if (c->h_meta->error & 1u) {
     return fail(c, NB_ERR_OVERFLOW,
@@ -916,6 +944,8 @@ int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {
   info->max_depth = c->n ? m.max_depth : 0;
   info->overflow_leaves = c->n ? m.overflow_leaves : 0;
   info->root_x0 = m.x0; info->root_y0 = m.y0; info->root_h = m.h;
+  info->sort_top_digits = c->n ? (uint32_t)c->last_top_passes : 0;
+  info->sort_redone = (c->n && c->last_top_passes) ? m.resort : 0;
   return NB_OK;
 }
 

@@ -8,6 +8,14 @@
 //              and writes coalesced runs.
 // HBM traffic: 8 B + passes x (12 B read + 12 B written) per pair  (6 passes: 152 B/pair).
 // Tiles take their index from an atomic ticket, so a tile only ever waits on tiles that already run.
+//
+// Top-digit (speculative) sort.  The tree only needs the bodies ordered down to the deepest leaf: inside a leaf
+// tree_finish_kernel orders them by body id whatever the sort left.  When the previous build's depth is known,
+// radix_sort_pairs runs just the top `top_passes` digits (a stable LSD sort of those digits), tree_count_kernel
+// checks that no leaf is deeper than the sorted prefix, and if one is (meta->resort) the passes that
+// radix_sort_fallback enqueued behind it — every kernel of them a no-op otherwise — sort the permuted pairs by the
+// full key.  A stable full sort of a stably top-sorted permutation is the stable full sort of the input, and the
+// plan has an even number of passes, so either way the result sits in the same buffer.
 #pragma once
 #include "common.cuh"
 #include "scan.cuh"
@@ -78,7 +86,10 @@ __global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restric
   uint32_t tot;
   const uint32_t ex = block_exclusive_scan<512>(v, tot);
   if ((int)threadIdx.x < radix) h[threadIdx.x] = ex;
-  if (threadIdx.x == 0) tickets[p] = 0;
+  if (threadIdx.x == 0) {
+    tickets[p] = 0;
+    tickets[kSortMaxPasses + 1 + p] = 0; // the fallback passes' tickets
+  }
   if (meta && p == plan.passes - 1) {
     if (plan.bits[p] == 9 && threadIdx.x == 256) meta->n_in = ex;
     if (threadIdx.x == 0) {
@@ -89,6 +100,7 @@ __global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restric
       meta->max_depth = 0;
       meta->overflow_leaves = 0;
       meta->cog_outside = 0;
+      meta->resort = 0;
     }
   }
 }
@@ -98,7 +110,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_onesweep_kernel(
     const unsigned long long *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
     unsigned long long *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int shift,
     const uint32_t *__restrict__ gbase /* scanned histogram of this pass */, uint32_t *ticket,
-    volatile uint32_t *status /* [tiles][RADIX], zeroed */) {
+    volatile uint32_t *status /* [tiles][RADIX], zeroed */, const uint32_t *cond /* run only if null or *cond != 0 */) {
+  if (cond && *cond == 0u) return;
   constexpr int RADIX = 1 << RADIX_BITS;
   constexpr int kSortTile = kSortThreads * kSortRounds;
   constexpr int DPT = RADIX / kSortThreads; // digits per thread in the look-back (1 or 2)
@@ -241,49 +254,92 @@ inline int sort_rounds_for(uint32_t n) { return n < (1u << 19) ? 8 : 16; }
 inline size_t sort_status_words(uint32_t n_max) {
   size_t tiles = ((size_t)n_max + 32 * 8 * kSortWarps - 1) / (32 * 8 * kSortWarps);
   if (tiles == 0) tiles = 1;
-  return tiles * (size_t)(5 * 256 + 512 + 256); // up to 7 passes, one of them 9 bits wide
+  return 2 * tiles * (size_t)(5 * 256 + 512 + 256); // up to 7 passes, one of them 9 bits wide; twice: top-digit passes + fallback
 }
 
-// Sorts the low `bits` key bits.  Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
+// One pass of the plan (p) from (kin, vin) to (kout, vout).
+inline void sort_enqueue_pass(const SortPlan &plan, int p, int rounds, uint32_t tiles, const unsigned long long *kin,
+                              const uint32_t *vin, unsigned long long *kout, uint32_t *vout, uint32_t n,
+                              const uint32_t *gb, uint32_t *ticket, uint32_t *status, const uint32_t *cond,
+                              cudaStream_t st) {
+#define NB_SORT_PASS(RB, RO)                                                                                   \
+  sort_onesweep_kernel<RB, RO><<<tiles, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, plan.shift[p], gb, ticket, \
+                                                               status, cond)
+  if (plan.bits[p] == 9) {
+    if (rounds == 8) NB_SORT_PASS(9, 8);
+    else NB_SORT_PASS(9, 16);
+  } else {
+    if (rounds == 8) NB_SORT_PASS(8, 8);
+    else NB_SORT_PASS(8, 16);
+  }
+#undef NB_SORT_PASS
+}
+
+// True if radix_sort_pairs(..., top_passes) + radix_sort_fallback is usable for this plan (see the header).
+inline bool sort_can_speculate(const SortPlan &plan, int top_passes) {
+  return top_passes > 0 && top_passes < plan.passes && (plan.passes % 2) == 0;
+}
+
+// Sorts the low `bits` key bits — or, with top_passes > 0, only the top `top_passes` digits of them (stable).
+// Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
 inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
                             uint32_t *vals_b, uint32_t n, int bits, const SortScratch &sc, cudaStream_t st,
-                            Meta *meta = nullptr) {
+                            Meta *meta = nullptr, int top_passes = 0) {
   if (n == 0) return 0;
   const SortPlan plan = make_sort_plan(bits);
   const int rounds = sort_rounds_for(n);
   const uint32_t tile_elems = (uint32_t)(kSortThreads * rounds);
   const uint32_t tiles = (n + tile_elems - 1) / tile_elems;
+  const bool spec = sort_can_speculate(plan, top_passes);
+  const int first = spec ? plan.passes - top_passes : 0;
   size_t need = 0;
-  for (int p = 0; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
+  for (int p = first; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
+  if (spec) // the fallback passes' look-back state
+    for (int p = 0; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
   cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);
   cudaMemsetAsync(sc.status, 0, need * sizeof(uint32_t), st);
   const uint32_t hblocks = tiles < (uint32_t)kSMs * 4u ? tiles : (uint32_t)kSMs * 4u;
-  g_launches += 2 + plan.passes;
+  g_launches += 2 + (plan.passes - first);
   sort_histogram_kernel<<<hblocks, 256, plan.hist_total * sizeof(uint32_t), st>>>(keys_a, n, plan, sc.ghist);
   sort_scan_hist_kernel<<<plan.passes, 512, 0, st>>>(sc.ghist, plan, sc.tickets, meta, n);
   unsigned long long *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
   int which = 0;
   size_t soff = 0;
-  for (int p = 0; p < plan.passes; ++p) {
-    const uint32_t *gb = sc.ghist + plan.hist_off[p];
-#define NB_SORT_PASS(RB, RO)                                                                                   \
-  sort_onesweep_kernel<RB, RO><<<tiles, kSortThreads, 0, st>>>(kin, vin, kout, vout, n, plan.shift[p], gb,     \
-                                                               sc.tickets + p, sc.status + soff)
-    if (plan.bits[p] == 9) {
-      if (rounds == 8) NB_SORT_PASS(9, 8);
-      else NB_SORT_PASS(9, 16);
-    } else {
-      if (rounds == 8) NB_SORT_PASS(8, 8);
-      else NB_SORT_PASS(8, 16);
-    }
-#undef NB_SORT_PASS
+  for (int p = first; p < plan.passes; ++p) {
+    sort_enqueue_pass(plan, p, rounds, tiles, kin, vin, kout, vout, n, sc.ghist + plan.hist_off[p], sc.tickets + p,
+                      sc.status + soff, nullptr, st);
     soff += (size_t)tiles << plan.bits[p];
     unsigned long long *tk = kin; kin = kout; kout = tk;
     uint32_t *tv = vin; vin = vout; vout = tv;
     which ^= 1;
   }
   return which;
+}
+
+// After radix_sort_pairs(..., top_passes) returned `which`: the full sort, every pass conditional on *cond
+// (= &meta->resort, raised by tree_count_kernel).  The result stays in buffer `which`.
+inline void radix_sort_fallback(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
+                                uint32_t *vals_b, int which, uint32_t n, int bits, int top_passes,
+                                const SortScratch &sc, cudaStream_t st, const uint32_t *cond) {
+  if (n == 0) return;
+  const SortPlan plan = make_sort_plan(bits);
+  if (!sort_can_speculate(plan, top_passes)) return;
+  const int rounds = sort_rounds_for(n);
+  const uint32_t tile_elems = (uint32_t)(kSortThreads * rounds);
+  const uint32_t tiles = (n + tile_elems - 1) / tile_elems;
+  size_t soff = 0;
+  for (int p = plan.passes - top_passes; p < plan.passes; ++p) soff += (size_t)tiles << plan.bits[p];
+  unsigned long long *kin = which ? keys_b : keys_a, *kout = which ? keys_a : keys_b;
+  uint32_t *vin = which ? vals_b : vals_a, *vout = which ? vals_a : vals_b;
+  g_launches += plan.passes;
+  for (int p = 0; p < plan.passes; ++p) {
+    sort_enqueue_pass(plan, p, rounds, tiles, kin, vin, kout, vout, n, sc.ghist + plan.hist_off[p],
+                      sc.tickets + kSortMaxPasses + 1 + p, sc.status + soff, cond, st);
+    soff += (size_t)tiles << plan.bits[p];
+    unsigned long long *tk = kin; kin = kout; kout = tk;
+    uint32_t *tv = vin; vin = vout; vout = tv;
+  }
 }
 
 } // namespace nb

@@ -43,8 +43,12 @@ template <int NT> __device__ __forceinline__ uint32_t block_exclusive_scan(uint3
 }
 
 // Single block: exclusive scan of the block sums in place; total -> *total_out.
+// cond (optional): run only if *cond != 0.  stats (optional): when the build is about to be redone from a full sort
+// (stats->resort, see radix_sort.cuh), clear the statistics the first tree_count_kernel pass accumulated.
 __global__ void __launch_bounds__(1024) scan_bsum_kernel(uint32_t *__restrict__ bsum, uint32_t nb,
-                                                         uint32_t *total_out) {
+                                                         uint32_t *total_out, Meta *stats = nullptr,
+                                                         const uint32_t *cond = nullptr) {
+  if (cond && *cond == 0u) return;
   __shared__ uint32_t carry_s;
   if (threadIdx.x == 0) carry_s = 0;
   __syncthreads();
@@ -60,6 +64,11 @@ __global__ void __launch_bounds__(1024) scan_bsum_kernel(uint32_t *__restrict__ 
     __syncthreads();
   }
   if (threadIdx.x == 0 && total_out) *total_out = carry_s;
+  if (threadIdx.x == 0 && stats && stats->resort) {
+    stats->n_leaves = 0;
+    stats->overflow_leaves = 0;
+    stats->max_depth = 0;
+  }
 }
 
 } // namespace nb

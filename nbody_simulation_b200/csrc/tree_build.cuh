@@ -88,7 +88,13 @@ template <int BPL, bool COMPRESS>
 __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long long *__restrict__ skeys, Meta *meta,
                                                          int cap, uint8_t *__restrict__ leafdepth,
                                                          uint32_t *__restrict__ nstart,
-                                                         uint32_t *__restrict__ btotal) {
+                                                         uint32_t *__restrict__ btotal, int sorted_levels = 0,
+                                                         const uint32_t *cond = nullptr) {
+  // sorted_levels > 0: the keys are sorted by their top `sorted_levels` levels only (radix_sort.cuh).  Everything
+  // below is unaffected as long as every leaf is at most that deep, i.e. no window of cap + 1 consecutive bodies
+  // shares a prefix of sorted_levels or more; a window that does raises meta->resort, and the passes enqueued
+  // behind this one (cond = &meta->resort) redo the sort in full and this count.
+  if (cond && *cond == 0u) return;
   const uint32_t n_in = meta->n_in;
   const uint32_t i0 = blockIdx.x * blockDim.x;
   const uint32_t i = i0 + threadIdx.x;
@@ -101,7 +107,9 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
   __syncthreads();
   for (int t = threadIdx.x; t < 256 + cap; t += 256) {
     const long long j = (long long)i0 - cap + t;
-    s_w[t] = (j >= 0 && j + cap < (long long)n_in) ? (int8_t)cpl<BPL>(s_k[t], s_k[t + cap]) : (int8_t)-1;
+    const int8_t wp = (j >= 0 && j + cap < (long long)n_in) ? (int8_t)cpl<BPL>(s_k[t], s_k[t + cap]) : (int8_t)-1;
+    s_w[t] = wp;
+    if (sorted_levels > 0 && wp >= sorted_levels) meta->resort = 1u;
   }
   __syncthreads();
   uint32_t cnt = 0, isleaf = 0, over = 0;

@@ -314,3 +314,57 @@ def test_device_scene_generation_matches_host(sc, kind):
         assert d.max() <= 1 and int((d != 0).sum()) <= 5, (k, int(d.max()), int((d != 0).sum()))
     assert np.array_equal(q["weight"], p["weight"]) and not q["vx"].any() and not q["vy"].any()
     w.close()
+
+
+# ---- top-digit (speculative) sort of the quadtree build: radix_sort.cuh ---------------------------------------
+@pytest.mark.parametrize("sc,n", [("disc", 200_000), ("plummer", 150_000), ("galaxy", 120_001), ("default", 0)])
+def test_top_digit_sort_builds_the_same_tree(sc, n):
+    # the first build of a context sorts every digit (no depth known yet); the second sorts only the top digits the
+    # first one's depth calls for and checks the guess on the device: same tree, bit for bit, as the oracle's
+    p = scene(sc, n)
+    o = ob.Tree(ob.KIND_PIPE_QUAD, p["x"], p["y"], p["weight"]).export()
+    w = nb.World(len(p))
+    w.set_particles(p)
+    w.build_tree()
+    first = w.tree_info()
+    assert first.sort_top_digits == 0
+    w.set_particles(p)
+    w.build_tree()
+    info = w.tree_info()
+    want = max(2, (first.max_depth + 1 + 3) // 4)  # 4 quadtree levels per key digit, one level of margin
+    assert info.sort_top_digits == (want if want < 6 else 0) and info.sort_redone == 0, (want, info.sort_top_digits)
+    assert_tree_equal(w.tree(), o, f"{sc}/top-digit sort")
+    f = nb.World(len(p), full_sort=True)
+    f.set_particles(p)
+    f.build_tree()
+    f.set_particles(p)
+    f.build_tree()
+    assert f.tree_info().sort_top_digits == 0
+    assert_tree_equal(f.tree(), o, f"{sc}/full sort")
+    w.close()
+    f.close()
+
+
+def test_top_digit_sort_falls_back_when_the_guess_is_too_shallow():
+    shallow, deep = scene("disc", 20_000), scene("plummer", 150_000)
+    w = nb.World(len(deep), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(shallow)
+    w.build_tree()
+    d0 = w.tree_info().max_depth
+    w.set_particles(deep)  # much deeper than the previous build: the guess (from d0) cannot hold
+    c = nb.Counting()
+    ax, ay = w.accel(c)
+    info = w.tree_info()
+    assert info.max_depth > 4 * info.sort_top_digits >= d0, (d0, info.sort_top_digits, info.max_depth)
+    assert info.sort_redone == 1
+    T = ob.Tree(ob.KIND_PIPE_QUAD, deep["x"], deep["y"], deep["weight"])
+    assert_tree_equal(w.tree(), T.export(), "fallback to the full sort")
+    rx, ry, ni, nt, _ = T.accel(0.5)
+    assert int(c.interactions) == ni and int(c.node_tests) == nt
+    assert np.array_equal(bits(ax), bits(rx)) and np.array_equal(bits(ay), bits(ry))
+    w.set_particles(deep)  # now the depth is known: the guess holds
+    w.build_tree()
+    info = w.tree_info()
+    assert info.sort_redone == 0 and info.sort_top_digits * 4 >= info.max_depth
+    assert_tree_equal(w.tree(), T.export(), "after the fallback")
+    w.close()
