@@ -69,10 +69,23 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "10"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
+
+    def wait_first_sample(self, timeout=8.0):
+        """nvidia-smi needs a few hundred ms to start; the timed region of the default run is shorter than that."""
+        if self.p is None:
+            return
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < timeout:
+            try:
+                if os.path.getsize(self.f.name) > 0:
+                    return
+            except OSError:
+                return
+            time.sleep(0.01)
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
@@ -249,6 +262,11 @@ def main():
     # ---- interaction count of the timed steps: an identical (deterministic) replay with the diagnostic
     # counters compiled in; the timed runs below execute the production kernels (counters compiled out,
     # the reference never counted either).
+    # the clock sampler runs from here to the end of the e2e loop: counter replay, warm-up, the timed steps and the
+    # e2e steps are the same workload back to back (the timed region alone can be shorter than one sample period)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.wait_first_sample()
     warm = max(3, args.warmup)
     w.step(warm)
     cc = nb.Counting()
@@ -260,7 +278,6 @@ def main():
     # ---- device-resident throughput -----------------------------------------------------------------
     w.step(warm)
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     c = nb.Counting()
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -300,6 +317,8 @@ def main():
         del host, owner
 
     clocks = sampler.stop() if sampler else None
+    if clocks is not None:
+        clocks["window"] = "counter replay, warm-up, timed steps and e2e steps (nvidia-smi -lms 10, median)"
     if rank == 0:
         peaks, peak_src = measured_peaks()
         fmax = float(peaks.get("sm_max_mhz", 1965.0))

@@ -16,7 +16,8 @@ constexpr unsigned long long kKeyOut = 1ull << 48; // body outside the root squa
 // Device-resident per-step metadata: every kernel of a step reads its sizes from here, so a step
 // is enqueued without a single host synchronisation.
 struct Meta {
-  float x0, y0, h, _padf;   // root square (Rectangle::new(offset, height), quad_tree.rs:15-21)
+  float x0, y0, h;          // root square (Rectangle::new(offset, height), quad_tree.rs:15-21)
+  float theta2;             // THETA * THETA (f32 product), written by the host: nb_create / nb_set_params
   uint32_t n;               // bodies
   uint32_t n_in;            // bodies in the tree (sorted positions [0, n_in))
   uint32_t n_nodes;
@@ -26,6 +27,7 @@ struct Meta {
   uint32_t error;           // bit 0: node pool too small
   uint32_t cog_outside;     // != 0: some internal node's centre of gravity lies outside its box
   uint32_t resort;          // != 0: the top-digit sort of this step was too shallow for the tree (radix_sort.cuh)
+  uint32_t one;             // 1, written by the host: a loop bound the compiler cannot see through (traverse.cuh)
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)
 };

@@ -152,6 +152,13 @@ template <class Tp> cudaError_t dmalloc(Tp **p, size_t count) { return cudaMallo
 
 inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 
+// THETA * THETA as one f32 product (rounded once): the bits a device FMUL of the same operands gives.
+inline float theta_squared(float theta) {
+  const volatile float t = theta;
+  const volatile float t2 = t * t;
+  return t2;
+}
+
 int alloc_bodies(nb_ctx *c, BodyArrays &b, size_t n) {
   NB_CUDA(c, dmalloc(&b.x, n));
   NB_CUDA(c, dmalloc(&b.y, n));
@@ -315,10 +322,8 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
                                                           c->cfg.theta, first, count)
 #define NB_TRAVERSE_FAST(CNT)                                                                                     \
   traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
-                                                           theta2, first, count)
+                                                           first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
-  const volatile float theta_f = c->cfg.theta;
-  const float theta2 = theta_f * theta_f; // f32 product, rounded once: the bits the device's FMUL would give
   if (ex && c->counting) NB_TRAVERSE(true, true);
   else if (ex) NB_TRAVERSE(true, false);
   else if (c->counting) NB_TRAVERSE_FAST(true);
@@ -649,6 +654,8 @@ nb_ctx *nb_create(const nb_config *cfg) {
   }
   Meta m0{};
   m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;
+  m0.theta2 = theta_squared(c->cfg.theta);
+  m0.one = 1u;
   NB_TRY(cudaMemcpy(c->meta, &m0, sizeof(Meta), cudaMemcpyHostToDevice));
   *c->h_meta = m0;
 #undef NB_TRY
@@ -661,6 +668,10 @@ int nb_set_params(nb_ctx *c, float theta, float dt, int32_t force_mode) {
   c->cfg.theta = theta;
   c->cfg.dt = dt;
   c->cfg.force_mode = force_mode;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  const float t2 = theta_squared(theta); // stream-ordered: kernels already enqueued keep the old value
+  NB_CUDA(c, cudaMemcpyAsync(&c->meta->theta2, &t2, sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  c->h_meta->theta2 = t2;
   return NB_OK;
 }
 

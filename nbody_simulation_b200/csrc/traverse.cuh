@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 template <bool COUNT, bool CONTAINS>
 __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
                                                    Meta *meta, const float4 *__restrict__ sbody,
-                                                   float2 *__restrict__ sacc, const float theta2_in, uint32_t tfirst,
+                                                   float2 *__restrict__ sacc, const float theta2, uint32_t tfirst,
                                                    uint32_t tcount) {
   const unsigned lane = threadIdx.x & 31;
   const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
@@ -200,14 +200,10 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   uint32_t resume = valid ? 0u : 0xffffffffu;
   uint32_t n_inter = 0, n_test = 0;
   const uint32_t n_nodes = meta->n_nodes;
-  // theta^2 is made to depend on loaded data (n_nodes < 2^31, so the shift adds 0): ptxas then keeps it in a
-  // register; as a plain kernel parameter it is re-read from the constant bank on every visit, and the kernel
-  // is bound by issue slots.
-  const float theta2 = __uint_as_float(__float_as_uint(theta2_in) + (n_nodes >> 31));
   // The odd first body of a leaf must stay behind a (warp-uniform) branch: ptxas if-converts `if (k & 1)` into 16
-  // predicated issue slots on every even leaf.  `one` is 1 (same n_nodes < 2^31 argument), but not provably so,
-  // which keeps the loop over `k & one` a real loop.
-  const uint32_t one = 1u + ((n_nodes >> 31) << 8);
+  // predicated issue slots on every even leaf.  Meta::one is 1, but only the host knows: a loop over `k & one`
+  // stays a real loop.
+  const uint32_t one = meta->one;
   const float2 np = make_float2(-px, -py);
   uint32_t cur = 0;
   while (cur < n_nodes) {
@@ -238,16 +234,17 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
         // Bodies are summed in index order: an odd first body alone, then pairs.  The loop is kept rolled on
         // purpose: leaves hold 4-5 bodies on average, and the dispatch code of an unrolled loop with remainder
         // loops cost more issue slots per visit than it saved.
-        const float4 *bp = sbody + l.y;
+        uint32_t jb = l.y;
         float lx = ax, ly = ay; // continue the lane's own running sum: same summation order as the scalar walk
 #pragma unroll 1
         for (uint32_t o = k & one; o != 0u; --o) { // at most one trip; see `one`
-          const float4 b0 = *bp++;
+          const float4 b0 = sbody[jb++];
           const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), np);
           const float dx0 = e0.x, dy0 = e0.y;
           const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
           lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
         }
+        const float4 *bp = sbody + jb;
 #pragma unroll 1
         for (uint32_t j = k >> 1; j != 0u; --j, bp += 2) {
           const float4 b0 = bp[0];
@@ -291,15 +288,17 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   }
 }
 
-// theta2 = theta * theta comes in as a kernel parameter (the host's f32 product has the same bits as the device's):
-// the walk then multiplies by a constant-bank operand, where a register copy was being recomputed on every visit.
+// theta^2 is read from device memory (Meta::theta2, written by the host) rather than passed as a kernel parameter:
+// ptxas re-reads a parameter from the constant bank — or re-multiplies theta * theta — on every node visit, one
+// issue slot each time in a kernel bound by issue slots; a value loaded from global memory stays in its register.
 template <bool COUNT>
 __global__ void __launch_bounds__(256) traverse_fast_kernel(const float4 *__restrict__ box,
                                                             const float4 *__restrict__ node, Meta *meta,
                                                             const float4 *__restrict__ sbody,
-                                                            float2 *__restrict__ sacc, float theta2, uint32_t tfirst,
+                                                            float2 *__restrict__ sacc, uint32_t tfirst,
                                                             uint32_t tcount) {
   if (meta->error) return;
+  const float theta2 = meta->theta2;
   // Rectangle::contains is needed unless provably implied (kThetaSqNoContains)
   if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0)
     traverse_fast_body<COUNT, true>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
