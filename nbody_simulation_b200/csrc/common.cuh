@@ -30,6 +30,7 @@ struct Meta {
   uint32_t one;             // 1, written by the host: a loop bound the compiler cannot see through (traverse.cuh)
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)
+  const void *node_base;           // TreeArrays::node again, for the traversal to LOAD rather than take as a parameter (traverse.cuh)
 };
 
 // Common prefix length of two sorted 48-bit keys, in tree levels of BPL bits each.

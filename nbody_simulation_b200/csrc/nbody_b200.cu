@@ -656,6 +656,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;
   m0.theta2 = theta_squared(c->cfg.theta);
   m0.one = 1u;
+  m0.node_base = c->T.node;
   NB_TRY(cudaMemcpy(c->meta, &m0, sizeof(Meta), cudaMemcpyHostToDevice));
   *c->h_meta = m0;
 #undef NB_TRY

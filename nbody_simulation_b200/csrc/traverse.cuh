@@ -204,6 +204,11 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   // predicated issue slots on every even leaf.  Meta::one is 1, but only the host knows: a loop over `k & one`
   // stays a real loop.
   const uint32_t one = meta->one;
+  // The same goes for the node array's base (Meta::node_base holds the value of the `node` argument): as a kernel
+  // parameter it costs an LDC.64 per node visit.  (Doing it for `sbody` too tips ptxas into running the walk's
+  // bookkeeping on the uniform datapath, with R2UR / UR-to-R moves in the leaf loop: measured by instruction count,
+  // worse.)
+  node = static_cast<const float4 *>(meta->node_base);
   const float2 np = make_float2(-px, -py);
   uint32_t cur = 0;
   while (cur < n_nodes) {
