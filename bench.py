@@ -74,7 +74,7 @@ class ClockSampler:
         except Exception:
             self.p = None
 
-    def wait_first_sample(self, timeout=8.0):
+    def wait_first_sample(self, timeout=5.0):
         """nvidia-smi needs a few hundred ms to start; the timed region of the default run is shorter than that."""
         if self.p is None:
             return
@@ -267,6 +267,7 @@ def main():
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.wait_first_sample()
+    barrier()  # rank 0 may have waited for nvidia-smi: nobody starts stepping (and waiting on peers) before it is back
     warm = max(3, args.warmup)
     w.step(warm)
     cc = nb.Counting()

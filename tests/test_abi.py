@@ -35,6 +35,12 @@ def test_abi_version_and_struct_sizes():
     assert C.sizeof(_lib.NbConfig) == 88  # 84 bytes of fields, 8-byte aligned
     assert C.sizeof(_lib.NbCounting) == 5 * 8 + 7 * 8
     assert C.sizeof(_lib.NbTreeInfo) == 4 * 8 + 2 * 4 + 3 * 4 + 5 * 4
+    # fields carved out of the reserved words (ABI version unchanged: old callers passed / read zeros there)
+    assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.reserved.offset == 56
+    assert _lib.NbTreeInfo.sort_top_digits.offset == 52 and _lib.NbTreeInfo.sort_redone.offset == 56
+    cfg = _lib.NbConfig()
+    L.nb_default_config(C.byref(cfg), 10)
+    assert cfg.full_sort == 0 and not any(cfg.reserved)
 
 
 def test_default_config_is_the_reference_constants():
