@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 
 // FAST-mode kernel (NB_FORCE_FAST): same walk, same per-lane decisions, written for issue slots.
 //  * accepted interactions are plain predicated code (no vote guard around them);
-//  * a terminal visit runs a warp-uniform body loop, two bodies per trip plus an odd tail; every lane
+//  * a terminal visit runs a warp-uniform body loop, an odd first body and then two bodies per trip; every lane
 //    continues its running sum through the leaf in a copy and only the lanes that take the leaf (not masked,
 //    did not accept the twig) keep the copy — no divergent branch, no per-body predicate or select;
 //  * summation order inside a lane is unchanged (tree order): with ~2e4 interactions per body on the
@@ -201,9 +201,9 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
   uint32_t n_inter = 0, n_test = 0;
   const uint32_t n_nodes = meta->n_nodes;
   // The odd first body of a leaf must stay behind a (warp-uniform) branch: ptxas if-converts `if (k & 1)` into 16
-  // predicated issue slots on every even leaf.  Meta::one is 1, but only the host knows: a loop over `k & one`
-  // stays a real loop.
-  const uint32_t one = meta->one;
+  // predicated issue slots on every even leaf.  `one` is 1 (Meta::one is 0 or 1: its top bit is clear), but only the
+  // host knows: as far as ptxas can tell `k & one` may exceed 1, so the loop over it stays a real loop.
+  const uint32_t one = 1u | ((meta->one >> 31) << 8);
   // The same goes for the node array's base (Meta::node_base holds the value of the `node` argument): as a kernel
   // parameter it costs an LDC.64 per node visit.  (Doing it for `sbody` too tips ptxas into running the walk's
   // bookkeeping on the uniform datapath, with R2UR / UR-to-R moves in the leaf loop: measured by instruction count,
