@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
+    ap.add_argument("--full-sort", action="store_true",
+                    help="quadtree: sort every key digit in every build (default: only the digits the tree depth needs, "
+                         "checked on the device each step; same tree either way)")
     return ap.parse_args()
 
 
@@ -227,7 +230,8 @@ def main():
     n_total = len(parts)
     tree = {"quad": nb.NB_TREE_QUAD, "lbvh": nb.NB_TREE_LBVH, "bvhref": nb.NB_TREE_BVH_REF}[args.tree]
     force = nb.NB_FORCE_FAST if args.force == "fast" else nb.NB_FORCE_EXACT
-    w = nb.World(n_total, theta=args.theta, dt=0.1, tree=tree, force_mode=force, device=local_rank)
+    w = nb.World(n_total, theta=args.theta, dt=0.1, tree=tree, force_mode=force, device=local_rank,
+                 full_sort=args.full_sort)
     if world > 1:
         uid = torch.zeros(nb._lib.NB_UNIQUE_ID_BYTES, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -318,6 +322,13 @@ def main():
         del host, owner
 
     clocks = sampler.stop() if sampler else None
+    # what the builds of the timed steps sorted (one more build of the final state, outside every timed region)
+    w.build_tree()
+    ti = w.tree_info()
+    sort_note = ("n/a" if args.tree == "bvhref" else "every key digit" if ti.sort_top_digits == 0 else
+                 f"top {ti.sort_top_digits} of 6 key digits per build, the depth guess checked on the device in every step "
+                 f"and redone in full when too shallow (last build redone: {bool(ti.sort_redone)}); same tree bit for bit "
+                 "as the full sort (tests/test_gpu_parity.py::test_top_digit_sort_*), --full-sort turns it off")
     if clocks is not None:
         clocks["window"] = "counter replay, warm-up, timed steps and e2e steps (nvidia-smi -lms 10, median)"
     if rank == 0:
@@ -342,7 +353,8 @@ def main():
             "config": {"workload": workload_name(args, n_total), "n_bodies": n_total, "theta": args.theta,
                        "tree": args.tree, "force_mode": args.force, "parallelism": f"morton-range x{world}" + (f", exchange={args.exchange}" if world > 1 else ""),
                        "l2": "not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps",
-                       "interaction_count": "from an identical replay of the timed steps with counters on"},
+                       "interaction_count": "from an identical replay of the timed steps with counters on",
+                       "sort": sort_note, "tree_depth": int(ti.max_depth)},
             "steps_per_s": args.steps / dev_s,
             "interactions_per_step": inter / args.steps,
             "phases_ms": {"build": c.build_bvh / args.steps * 1e3, "traverse": trav_s * 1e3,
