@@ -22,6 +22,7 @@
 #include "radix_sort.cuh"
 #include "scan.cuh"
 #include "traverse.cuh"
+#include "traverse_group.cuh"
 #include "ubench.cuh"
 #include "tree_build.cuh"
 #include "bvh_ref.cuh"
@@ -296,7 +297,7 @@ int enqueue_build(nb_ctx *c) {
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
   if (!c->quad || !emit_links) g_launches += 1;
-  if (!c->quad) tree_link_kernel<false><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
+  if (!c->quad) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   else if (!emit_links) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
   // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
@@ -324,6 +325,14 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
                                                            first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
+  if (!ex && !c->bvh_ref && !c->cfg.fast_walk_dfs) {
+    // list-then-evaluate group walk (traverse_group.cuh): quadtree and LBVH in NB_FORCE_FAST
+    const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);
+    if (c->counting)
+      traverse_group_kernel<true><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
+    else
+      traverse_group_kernel<false><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
+  } else
   if (ex && c->counting) NB_TRAVERSE(true, true);
   else if (ex) NB_TRAVERSE(true, false);
   else if (c->counting) NB_TRAVERSE_FAST(true);
@@ -619,7 +628,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->T.depth, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.bmax, (size_t)c->T.capacity));
   NB_TRY(dmalloc(&c->T.arrive, (size_t)c->T.capacity));
-  if (c->quad) NB_TRY(dmalloc(&c->T.kids, (size_t)c->T.capacity));
+  if (!c->bvh_ref) NB_TRY(dmalloc(&c->T.kids, (size_t)c->T.capacity)); // children table: up-sweep (quad) and traverse_group_kernel
   NB_TRY(dmalloc(&c->sbody, na));
   NB_TRY(dmalloc(&c->sacc, na));
   NB_TRY(dmalloc(&c->bounds_partial, (size_t)kSMs * 4));

@@ -1,0 +1,309 @@
+// traverse_group.cuh — K5 (NB_FORCE_FAST, quadtree / LBVH): list-then-evaluate Barnes-Hut traversal.
+//
+// Reference: World::bvh_sum_gravity (src/main.rs:349-386) per body, opening rule main.rs:370-372, pair force
+// main.rs:235-253.  Every body still makes ITS OWN accept / open decision for every node it meets, so each body
+// evaluates exactly the interaction set of its private recursive walk (counts equal the scalar walk's); what
+// changes against traverse_fast_kernel is who does the deciding and when the forces are evaluated:
+//
+//  * DECIDE, lane-parallel.  A warp owns 32 tree-order-adjacent bodies and their bounding box.  It pops up to 32
+//    (node, lane mask) entries from a shared-memory stack, ONE NODE PER LANE, and classifies each against the box:
+//    "every body accepts" when the node passes the opening test for the nearest point of the box, "every body
+//    opens" when it fails for the farthest corner.  Both are conservative (1e-5 relative margin against the f32
+//    rounding of the per-body test), so they return what each body would have decided.  Only nodes in between
+//    ("mixed", ~65 of ~470 per group on the 1M-body disc) take a warp-uniform visit in which every body of the
+//    entry's mask runs the reference test itself; the bodies that accept become the item's mask, the others the
+//    mask its children inherit.  One classification pass costs about as much as ONE node visit of the
+//    depth-first walk and handles 32 nodes.
+//  * STAGE.  Accepted nodes and the bodies of opened leaves (an opened twig hands over all its leaves' bodies at
+//    once) are copied into two shared-memory lists as (x, y, mass[, mask]) records: F for items every body of
+//    the group takes, P for items only some take.
+//  * EVALUATE, dense.  F is a plain loop, one broadcast LDS.128 per item and all 32 lanes live.  P is evaluated
+//    through per-lane bit words (see eval_partial): a lane runs only over the items of ITS mask.
+//
+// Summation order: items are added in list order, which is the stack's pop order, a deterministic function of the
+// group alone — not the depth-first order of the reference, so results equal the reference's only to rounding
+// (tests: <= 1e-5 normwise vs the oracle on the same tree; measured ~1e-7).  NB_FORCE_EXACT keeps the
+// depth-first kernel (bit-identical sums), and so does the reference's own tree (NB_TREE_BVH_REF), whose ~2e4
+// interactions per body leave no room for a reordering inside 1e-5.
+#pragma once
+#include "traverse.cuh"
+
+namespace nb {
+
+constexpr int kGrpWarps = 4;    // warps (= groups) per block
+constexpr int kGrpStack = 256;  // (node, mask) entries per warp
+constexpr int kGrpF = 128;      // full-mask items per warp
+constexpr int kGrpP = 128;      // partial-mask items per warp (4 words of 32)
+constexpr uint32_t kNoKid = 0xffffffffu;
+
+struct GrpSmem { // per warp: 6.5 KB
+  uint2 stack[kGrpStack];
+  float4 F[kGrpF];
+  float4 P[kGrpP];
+  uint32_t words[kGrpP / 32][32]; // words[c][lane]: bit i = lane takes item P[32 c + i]
+};
+
+// main.rs:235-253, FAST arithmetic (same instruction sequence as traverse_fast_kernel): np = (-px, -py)
+__device__ __forceinline__ void grp_force(const float x, const float y, const float m, const float2 np, float &ax,
+                                          float &ay) {
+  const float2 d = __fadd2_rn(make_float2(x, y), np);
+  const float w = m * rcp_approx(fmaf(fabsf(d.x) + fabsf(d.y), fmaxf(fmaf(d.y, d.y, d.x * d.x), 0.001f), 1e-20f));
+  ax = fmaf(d.x, w, ax);
+  ay = fmaf(d.y, w, ay);
+}
+
+__device__ __forceinline__ void eval_full(const float4 *__restrict__ F, const uint32_t n, const float2 np, float &ax,
+                                          float &ay) {
+#pragma unroll 4
+  for (uint32_t i = 0; i < n; ++i) {
+    const float4 it = F[i]; // all lanes read the same address: one broadcast wavefront
+    grp_force(it.x, it.y, it.z, np, ax, ay);
+  }
+}
+
+// 32 x 32 bit transpose across the warp: in: lane i holds row i; out: lane t holds column t (bit i = bit t of row i).
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, const unsigned lane) {
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    const uint32_t m = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu
+                     : (s == 2) ? 0x33333333u : 0x55555555u; // bits whose index has bit s clear
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s);
+    // lanes with bit s clear keep their low half-blocks and take the partner's low half-blocks into the high ones
+    x = (lane & s) ? ((x & ~m) | ((y >> s) & m)) : ((x & m) | ((y << s) & ~m));
+  }
+  return x;
+}
+
+// P items carry the mask of the lanes that take them in .w.  Each lane gets the bit column of ITS items (one
+// butterfly transpose per 32 items), then runs its own cursor over the words: a trip evaluates one item per
+// lane, whichever item the lane's next set bit names (LDS.128 gather), so the trip count is the LARGEST per-lane
+// item count instead of the number of items (mask density is ~40 %: 603 items, ~245 per lane on the 1M disc).
+__device__ __forceinline__ void eval_partial(GrpSmem &S, const uint32_t n, const unsigned lane, const float2 np,
+                                             float &ax, float &ay) {
+  const uint32_t nch = (n + 31u) >> 5;
+  uint32_t total = 0;
+  for (uint32_t c = 0; c < nch; ++c) {
+    const uint32_t i = c * 32u + lane;
+    const uint32_t row = i < n ? __float_as_uint(S.P[i].w) : 0u;
+    const uint32_t col = warp_transpose32(row, lane);
+    S.words[c][lane] = col;
+    total += __popc(col);
+  }
+  uint32_t trips = total;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) trips = max(trips, __shfl_xor_sync(0xffffffffu, trips, o));
+  uint32_t c = 0, w = S.words[0][lane];
+  for (uint32_t t = 0; t < trips; ++t) {
+    while (w == 0u && c + 1u < nch) w = S.words[++c][lane];
+    if (w) {
+      const uint32_t j = 31u - __clz(w);
+      w ^= 1u << j;
+      const float4 it = S.P[c * 32u + j];
+      grp_force(it.x, it.y, it.z, np, ax, ay);
+    }
+  }
+}
+
+template <bool COUNT, bool CONTAINS>
+__device__ __forceinline__ void traverse_group_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
+                                                    const uint4 *__restrict__ kids, Meta *meta,
+                                                    const float4 *__restrict__ sbody, float2 *__restrict__ sacc,
+                                                    const float theta2, const uint32_t tfirst, const uint32_t tcount,
+                                                    GrpSmem &S) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
+  if (t0 >= tcount) return;
+  const bool valid = (t0 + lane) < tcount;
+  const uint32_t t = tfirst + (valid ? (t0 + lane) : t0);
+  const float4 me = sbody[t];
+  const float px = me.x, py = me.y;
+  const float2 np = make_float2(-px, -py);
+  const uint32_t FULL = __ballot_sync(0xffffffffu, valid);
+  // bounding box of the group's bodies (fminf / fmaxf drop NaNs: a NaN body decides for itself in the mixed visits
+  // or follows the others; its sums are NaN either way, as in the scalar walk)
+  float gx0 = px, gx1 = px, gy0 = py, gy1 = py; // invalid lanes duplicate body t0
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    gx0 = fminf(gx0, __shfl_xor_sync(0xffffffffu, gx0, o));
+    gx1 = fmaxf(gx1, __shfl_xor_sync(0xffffffffu, gx1, o));
+    gy0 = fminf(gy0, __shfl_xor_sync(0xffffffffu, gy0, o));
+    gy1 = fmaxf(gy1, __shfl_xor_sync(0xffffffffu, gy1, o));
+  }
+  const float th_acc = theta2 * 0.99999f, th_open = theta2 * 1.00001f;
+  const uint32_t lt = (1u << lane) - 1u;
+  float ax = 0.f, ay = 0.f;
+  uint32_t n_inter = 0, n_test = 0;
+  uint32_t top = 0, fcnt = 0, pcnt = 0;
+  if (meta->n_nodes != 0u) {
+    if (lane == 0) S.stack[0] = make_uint2(0u, FULL);
+    top = 1;
+  }
+  __syncwarp();
+  while (top != 0u) {
+    // Pop up to 32 entries, fewer when the stack is nearly full: an entry pushes at most 4 children (net +3), and
+    // with one pop per round the walk is depth-first and needs 3 entries per level (<= 24 levels of 2-bit keys,
+    // 48 binary levels with net +1): 72 entries of headroom always suffice.
+    const int room = (kGrpStack - 72 - (int)top) / 3;
+    const uint32_t p = min(min(32u, top), (uint32_t)max(room, 1));
+    const bool have = lane < p;
+    uint2 e = make_uint2(0u, 0u);
+    if (have) e = S.stack[top - 1u - lane];
+    top -= p;
+    __syncwarp();
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 l = make_uint4(0u, 0u, 0u, 0u);
+    if (have) load_node(node + 2 * (size_t)e.x, c, l);
+    const uint32_t mask = e.y;
+    uint32_t accm = 0u, openm = 0u, rk = 0u, rmask = 0u;
+    bool mixed = false;
+    if (have) {
+      if (l.z & kLeafBit) { // main.rs:351-363: every body that reaches a leaf sums all its bodies
+        rk = l.z & kCountMask;
+        rmask = mask;
+      } else {
+        const float ux = gx0 - c.x, vx = c.x - gx1, uy = gy0 - c.y, vy = c.y - gy1;
+        const float nx = fmaxf(fmaxf(ux, vx), 0.f), ny = fmaxf(fmaxf(uy, vy), 0.f); // to the nearest point of the box
+        const float fx = fmaxf(-ux, -vx), fy = fmaxf(-uy, -vy);                     // to the farthest corner
+        const float dmin2 = fmaf(ny, ny, nx * nx), dmax2 = fmaf(fy, fy, fx * fx);
+        bool all_acc = c.w < dmin2 * th_acc;
+        if (CONTAINS) { // no body strictly inside the node's box (bvh_tree.rs:15-20) if the boxes do not overlap
+          const float4 bx = box[e.x];
+          all_acc = all_acc && (bx.z <= gx0 || bx.x >= gx1 || bx.w <= gy0 || bx.y >= gy1);
+        }
+        const bool all_open = !(c.w < dmax2 * th_open);
+        accm = all_acc ? mask : 0u;
+        openm = (!all_acc && all_open) ? mask : 0u;
+        mixed = !all_acc && !all_open;
+        if (COUNT) n_test += __popc(mask);
+      }
+    }
+    // mixed nodes: every body of the entry's mask runs main.rs:370-372 itself (FAST arithmetic)
+    uint32_t mb = __ballot_sync(0xffffffffu, mixed);
+    while (mb) {
+      const int j = __ffs(mb) - 1;
+      mb &= mb - 1u;
+      const float cx = __shfl_sync(0xffffffffu, c.x, j), cy = __shfl_sync(0xffffffffu, c.y, j);
+      const float s2 = __shfl_sync(0xffffffffu, c.w, j);
+      const uint32_t mk = __shfl_sync(0xffffffffu, mask, j);
+      const float2 d = __fadd2_rn(make_float2(cx, cy), np);
+      bool far = s2 < fmaf(d.y, d.y, d.x * d.x) * theta2;
+      if (CONTAINS) {
+        const float4 bx = box[__shfl_sync(0xffffffffu, e.x, j)];
+        far = far && !(py > bx.y && px > bx.x && px < bx.z && py < bx.w);
+      }
+      const uint32_t b = __ballot_sync(0xffffffffu, far) & mk;
+      if ((int)lane == j) {
+        accm = b;
+        openm = mk & ~b;
+      }
+    }
+    // an opened twig (all children are leaves) hands over every body below it, in tree order
+    if (openm != 0u && (l.z & kTwigBit)) {
+      rk = l.z & kCountMask;
+      rmask = openm;
+      openm = 0u;
+    }
+    if (COUNT) n_inter += __popc(accm) + rk * __popc(rmask);
+    { // accepted nodes -> F (every body of the group) or P (some)
+      const bool isF = accm == FULL && accm != 0u, isP = accm != 0u && !isF;
+      const uint32_t bf = __ballot_sync(0xffffffffu, isF), bp = __ballot_sync(0xffffffffu, isP);
+      if (fcnt + 32u > (uint32_t)kGrpF) {
+        __syncwarp();
+        eval_full(S.F, fcnt, np, ax, ay);
+        fcnt = 0;
+        __syncwarp();
+      }
+      if (pcnt + 32u > (uint32_t)kGrpP) {
+        __syncwarp();
+        eval_partial(S, pcnt, lane, np, ax, ay);
+        pcnt = 0;
+        __syncwarp();
+      }
+      if (isF) S.F[fcnt + __popc(bf & lt)] = make_float4(c.x, c.y, c.z, 0.f);
+      if (isP) S.P[pcnt + __popc(bp & lt)] = make_float4(c.x, c.y, c.z, __uint_as_float(accm));
+      fcnt += __popc(bf);
+      pcnt += __popc(bp);
+    }
+    { // children of opened nodes -> stack, with the mask of the bodies that opened the parent
+      uint4 kd = make_uint4(kNoKid, kNoKid, kNoKid, kNoKid);
+      if (openm != 0u) kd = kids[e.x];
+      const uint32_t kq[4] = {kd.x, kd.y, kd.z, kd.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const bool v = kq[q] != kNoKid;
+        const uint32_t b = __ballot_sync(0xffffffffu, v);
+        if (v) S.stack[top + __popc(b & lt)] = make_uint2(kq[q], openm);
+        top += __popc(b);
+      }
+    }
+    // body ranges (leaves, opened twigs): the warp copies each range, coalesced, into F or P
+    uint32_t rb = __ballot_sync(0xffffffffu, rk != 0u);
+    while (rb) {
+      const int j = __ffs(rb) - 1;
+      rb &= rb - 1u;
+      const uint32_t first = __shfl_sync(0xffffffffu, l.y, j), k = __shfl_sync(0xffffffffu, rk, j);
+      const uint32_t m = __shfl_sync(0xffffffffu, rmask, j);
+      for (uint32_t off = 0; off < k; off += 32u) {
+        const uint32_t nn = min(32u, k - off);
+        if (m == FULL) {
+          if (fcnt + 32u > (uint32_t)kGrpF) {
+            __syncwarp();
+            eval_full(S.F, fcnt, np, ax, ay);
+            fcnt = 0;
+            __syncwarp();
+          }
+          if (lane < nn) S.F[fcnt + lane] = sbody[first + off + lane];
+          fcnt += nn;
+        } else {
+          if (pcnt + 32u > (uint32_t)kGrpP) {
+            __syncwarp();
+            eval_partial(S, pcnt, lane, np, ax, ay);
+            pcnt = 0;
+            __syncwarp();
+          }
+          if (lane < nn) {
+            float4 b = sbody[first + off + lane];
+            b.w = __uint_as_float(m);
+            S.P[pcnt + lane] = b;
+          }
+          pcnt += nn;
+        }
+      }
+    }
+    __syncwarp();
+  }
+  eval_full(S.F, fcnt, np, ax, ay);
+  if (pcnt) eval_partial(S, pcnt, lane, np, ax, ay);
+  if (valid) sacc[t] = make_float2(ax, ay);
+  if (COUNT) {
+    unsigned long long wi = n_inter, wt = n_test;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      wi += __shfl_xor_sync(0xffffffffu, wi, o);
+      wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&meta->interactions, wi);
+      atomicAdd(&meta->node_tests, wt);
+    }
+  }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kGrpWarps * 32) traverse_group_kernel(const float4 *__restrict__ box,
+                                                                        const float4 *__restrict__ node,
+                                                                        const uint4 *__restrict__ kids, Meta *meta,
+                                                                        const float4 *__restrict__ sbody,
+                                                                        float2 *__restrict__ sacc, uint32_t tfirst,
+                                                                        uint32_t tcount) {
+  if (meta->error) return;
+  __shared__ GrpSmem smem[kGrpWarps];
+  GrpSmem &S = smem[threadIdx.x >> 5];
+  const float theta2 = meta->theta2;
+  if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0) // see kThetaSqNoContains
+    traverse_group_body<COUNT, true>(box, node, kids, meta, sbody, sacc, theta2, tfirst, tcount, S);
+  else
+    traverse_group_body<COUNT, false>(box, node, kids, meta, sbody, sacc, theta2, tfirst, tcount, S);
+}
+
+} // namespace nb
