@@ -10,6 +10,18 @@ struct BodyArrays {
   uint32_t *m, *id; // integer mass; original body index of the slot
 };
 
+// A step whose build failed (Meta::error: node pool overflow, peer time-out) must not advance the state with
+// stale accelerations and a stale order: the integrate kernels then copy every body to the same slot of the
+// other buffer, so the state stays that of the last good step.
+__device__ __forceinline__ void copy_body(const BodyArrays &in, const BodyArrays &out, uint32_t j) {
+  out.x[j] = in.x[j];
+  out.y[j] = in.y[j];
+  out.vx[j] = in.vx[j];
+  out.vy[j] = in.vy[j];
+  out.m[j] = in.m[j];
+  out.id[j] = in.id[j];
+}
+
 // Reference src/main.rs:419-423:  v += a*dt;  x += v*dt  (separate mul and add: Rust does not
 // contract).  Body j of the tree order is read from its old storage slot and written to slot j of
 // the other buffer, so the next step's storage is already Morton-ordered (coalesced writes, near-
@@ -18,10 +30,14 @@ struct BodyArrays {
 __global__ void __launch_bounds__(256) integrate_resort_kernel(const uint32_t *__restrict__ order,
                                                                const float2 *__restrict__ sacc, BodyArrays in,
                                                                BodyArrays out, uint32_t jfirst, uint32_t jcount,
-                                                               float dt) {
+                                                               float dt, const Meta *__restrict__ meta) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= jcount) return;
   const uint32_t j = jfirst + k;
+  if (meta->error) { // the build of this step failed: the state is carried over unchanged, slot for slot
+    copy_body(in, out, j);
+    return;
+  }
   const uint32_t s = order[j];
   const float2 a = sacc[j];
   const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
@@ -46,9 +62,14 @@ __global__ void __launch_bounds__(256) invert_order_kernel(const uint32_t *__res
 __global__ void __launch_bounds__(256) integrate_resort_bug_kernel(const uint32_t *__restrict__ order,
                                                                    const uint32_t *__restrict__ pos_of_slot,
                                                                    const float2 *__restrict__ sacc, BodyArrays in,
-                                                                   BodyArrays out, uint32_t n, float dt) {
+                                                                   BodyArrays out, uint32_t n, float dt,
+                                                                   const Meta *__restrict__ meta) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
+  if (meta->error) {
+    copy_body(in, out, j);
+    return;
+  }
   const uint32_t s = order[j];
   const float2 a = sacc[pos_of_slot[j]];
   const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
@@ -65,10 +86,10 @@ __global__ void __launch_bounds__(256) integrate_resort_bug_kernel(const uint32_
 // other ranks' bodies arrive by all-gather, mass and id are replicated and permuted locally).
 __global__ void __launch_bounds__(256) permute_mid_kernel(const uint32_t *__restrict__ order, BodyArrays in,
                                                           BodyArrays out, uint32_t n, uint32_t jfirst,
-                                                          uint32_t jcount) {
+                                                          uint32_t jcount, const Meta *__restrict__ meta) {
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n || (j >= jfirst && j < jfirst + jcount)) return;
-  const uint32_t s = order[j];
+  const uint32_t s = meta->error ? j : order[j];
   out.m[j] = in.m[s];
   out.id[j] = in.id[s];
 }
@@ -88,16 +109,17 @@ struct PeerFlags { uint32_t *flags[kMaxPeers]; }; // flags[r] = rank r's flag ar
 __global__ void __launch_bounds__(256) integrate_push_kernel(const uint32_t *__restrict__ order,
                                                              const float2 *__restrict__ sacc, BodyArrays in,
                                                              BodyArrays out, PeerOut po, int n_ranks, uint32_t jfirst,
-                                                             uint32_t jcount, float dt) {
+                                                             uint32_t jcount, float dt, const Meta *__restrict__ meta) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= jcount) return;
   const uint32_t j = jfirst + k;
-  const uint32_t s = order[j];
-  const float2 a = sacc[j];
-  const float vx = __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
-  const float vy = __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
-  const float x = __fadd_rn(in.x[s], __fmul_rn(vx, dt));
-  const float y = __fadd_rn(in.y[s], __fmul_rn(vy, dt));
+  const bool bad = meta->error != 0u; // failed build (the same on every rank): carry the state over unchanged
+  const uint32_t s = bad ? j : order[j];
+  const float2 a = bad ? make_float2(0.f, 0.f) : sacc[j];
+  const float vx = bad ? in.vx[s] : __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
+  const float vy = bad ? in.vy[s] : __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
+  const float x = bad ? in.x[s] : __fadd_rn(in.x[s], __fmul_rn(vx, dt));
+  const float y = bad ? in.y[s] : __fadd_rn(in.y[s], __fmul_rn(vy, dt));
   for (int r = 0; r < n_ranks; ++r) {
     po.vx[r][j] = vx;
     po.vy[r][j] = vy;

@@ -360,25 +360,25 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   if (c->cfg.faithful_index_bug && count) { // single GPU, NB_TREE_BVH_REF (checked in nb_create / nb_comm_init)
     uint32_t *pos_of_slot = c->vals[c->sorted_in ^ 1];
     invert_order_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, n, pos_of_slot);
-    integrate_resort_bug_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, pos_of_slot, c->sacc, in, out, n, dt);
+    integrate_resort_bug_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, pos_of_slot, c->sacc, in, out, n, dt, c->meta);
     g_launches += 1;
   } else if (count && !(c->n_ranks > 1 && c->peer))
-    integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt);
+    integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt, c->meta);
   if (c->n_ranks > 1 && c->peer) {
     // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here
     if (count)
       integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, c->peer_out[c->cur ^ 1],
-                                                                    c->n_ranks, first, count, dt);
-    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
+                                                                    c->n_ranks, first, count, dt, c->meta);
+    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
     ++c->peer_epoch;
     g_launches += 2;
     peer_signal_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags_of, c->n_ranks, c->rank, c->peer_epoch);
     peer_wait_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags, c->n_ranks, c->peer_epoch, c->meta);
   } else if (c->n_ranks > 1) {
-    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count);
+    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
-    const size_t per = cdiv(n, (uint32_t)c->n_ranks);
+    const size_t per = (size_t)cdiv(cdiv(n, (uint32_t)c->n_ranks), 32u) * 32u; // == nb_shard_range
     ncclResult_t r;
     if ((r = g_nccl.GroupStart()) != ncclSuccess) return nccl_fail(c, r, "ncclGroupStart");
     float *arrs[4] = {out.x, out.y, out.vx, out.vy};
@@ -606,7 +606,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   if ((e = (call)) != cudaSuccess) return bail(#call, e)
   NB_TRY(cudaSetDevice(c->device));
   NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  const size_t na = ((size_t)cfg->n_max + 64 + 1023) / 1024 * 1024;
+  const size_t na = ((size_t)cfg->n_max + 64 + 32 * kMaxPeers + 1023) / 1024 * 1024; // + the all-gather's rounded-up slices
   c->n_alloc = (uint32_t)na;
   for (int i = 0; i < 2; ++i) {
     if (alloc_bodies(c, c->body[i], na) != NB_OK) { g_create_error = c->err; nb_destroy(c); return nullptr; }
@@ -1196,7 +1196,9 @@ void nb_shard_range(uint64_t n, int rank, int n_ranks, uint64_t *first, uint64_t
     *count = n;
     return;
   }
-  const uint64_t per = (n + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks;
+  // whole 32-body groups: traverse_group_kernel's sums depend on which 32 bodies share a warp, so shard starts are
+  // multiples of 32 and every rank forms the groups a single GPU forms (state bit-identical to one GPU)
+  const uint64_t per = ((n + (uint64_t)n_ranks - 1) / (uint64_t)n_ranks + 31u) / 32u * 32u;
   const uint64_t f = std::min<uint64_t>(n, per * (uint64_t)rank);
   *first = f;
   *count = std::min<uint64_t>(per, n - f);

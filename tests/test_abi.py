@@ -36,7 +36,7 @@ def test_abi_version_and_struct_sizes():
     assert C.sizeof(_lib.NbCounting) == 5 * 8 + 7 * 8
     assert C.sizeof(_lib.NbTreeInfo) == 4 * 8 + 2 * 4 + 3 * 4 + 5 * 4
     # fields carved out of the reserved words (ABI version unchanged: old callers passed / read zeros there)
-    assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.reserved.offset == 56
+    assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.fast_walk_dfs.offset == 56 and _lib.NbConfig.reserved.offset == 60
     assert _lib.NbTreeInfo.sort_top_digits.offset == 52 and _lib.NbTreeInfo.sort_redone.offset == 56
     cfg = _lib.NbConfig()
     L.nb_default_config(C.byref(cfg), 10)
@@ -113,5 +113,6 @@ def test_shard_rule():
             for f, c in spans:
                 assert f == pos or c == 0
                 pos += c
-            per = -(-n // g) if g > 1 else n
+            per = -(-(-(-n // g)) // 32) * 32 if g > 1 else n  # ceil(n / g) rounded up to whole 32-body warps
             assert all(c <= per for _, c in spans)
+            assert all(f % 32 == 0 for f, c in spans if c)

@@ -38,7 +38,7 @@ def _worker(rank, world, port, n, steps, kind, out_dir):
     # replicated slot-order state (slot order == tree order of the previous step)
     x, y, vx, vy = (p[k].copy() for k in ("x", "y", "vx", "vy"))
     m, ident = p["weight"].copy(), np.arange(n, dtype=np.uint32)
-    per = -(-n // world)
+    per = -(-(-(-n // world)) // 32) * 32  # nb_shard_range: whole 32-body warps
     for _ in range(steps):
         T = ob.Tree(kind, x, y, m)
         order = T.export()["order"]  # tree position -> slot
