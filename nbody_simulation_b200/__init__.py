@@ -99,7 +99,7 @@ class World:
 
     def __init__(self, n_max, theta=THETA, dt=STEP_SIZE, tree=NB_TREE_QUAD, leaf_cap=0,
                  domain=(0.0, 0.0, float(HEIGHT)), domain_auto=False, force_mode=NB_FORCE_FAST, device=0,
-                 faithful_index_bug=False, full_sort=False, fast_walk_dfs=False):
+                 faithful_index_bug=False, full_sort=False, fast_walk_group=False):
         self._L = _lib.lib()
         cfg = NbConfig()
         self._L.nb_default_config(C.byref(cfg), int(n_max))
@@ -110,7 +110,7 @@ class World:
         cfg.force_mode, cfg.device = int(force_mode), int(device)
         cfg.faithful_index_bug = 1 if faithful_index_bug else 0
         cfg.full_sort = 1 if full_sort else 0
-        cfg.fast_walk_dfs = 1 if fast_walk_dfs else 0
+        cfg.fast_walk_group = 1 if fast_walk_group else 0
         self.cfg = cfg
         self._ctx = self._L.nb_create(C.byref(cfg))
         if not self._ctx:

@@ -40,7 +40,7 @@ class NbConfig(C.Structure):
         ("device", C.c_int32),
         ("faithful_index_bug", C.c_int32),
         ("full_sort", C.c_int32),
-        ("fast_walk_dfs", C.c_int32),
+        ("fast_walk_group", C.c_int32),
         ("reserved", C.c_int32 * 6),
     ]
 

@@ -325,7 +325,7 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
                                                            first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
-  if (!ex && !c->bvh_ref && !c->cfg.fast_walk_dfs) {
+  if (!ex && !c->bvh_ref && c->cfg.fast_walk_group) {
     // list-then-evaluate group walk (traverse_group.cuh): quadtree and LBVH in NB_FORCE_FAST
     const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);
     if (c->counting)

@@ -61,46 +61,14 @@ __device__ __forceinline__ void eval_full(const float4 *__restrict__ F, const ui
   }
 }
 
-// 32 x 32 bit transpose across the warp: in: lane i holds row i; out: lane t holds column t (bit i = bit t of row i).
-__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, const unsigned lane) {
-#pragma unroll
-  for (int s = 16; s > 0; s >>= 1) {
-    const uint32_t m = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu
-                     : (s == 2) ? 0x33333333u : 0x55555555u; // bits whose index has bit s clear
-    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, s);
-    // lanes with bit s clear keep their low half-blocks and take the partner's low half-blocks into the high ones
-    x = (lane & s) ? ((x & ~m) | ((y >> s) & m)) : ((x & m) | ((y << s) & ~m));
-  }
-  return x;
-}
-
-// P items carry the mask of the lanes that take them in .w.  Each lane gets the bit column of ITS items (one
-// butterfly transpose per 32 items), then runs its own cursor over the words: a trip evaluates one item per
-// lane, whichever item the lane's next set bit names (LDS.128 gather), so the trip count is the LARGEST per-lane
-// item count instead of the number of items (mask density is ~40 %: 603 items, ~245 per lane on the 1M disc).
+// P items carry the mask of the lanes that take them in .w: broadcast load, per-lane predicate.
 __device__ __forceinline__ void eval_partial(GrpSmem &S, const uint32_t n, const unsigned lane, const float2 np,
                                              float &ax, float &ay) {
-  const uint32_t nch = (n + 31u) >> 5;
-  uint32_t total = 0;
-  for (uint32_t c = 0; c < nch; ++c) {
-    const uint32_t i = c * 32u + lane;
-    const uint32_t row = i < n ? __float_as_uint(S.P[i].w) : 0u;
-    const uint32_t col = warp_transpose32(row, lane);
-    S.words[c][lane] = col;
-    total += __popc(col);
-  }
-  uint32_t trips = total;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) trips = max(trips, __shfl_xor_sync(0xffffffffu, trips, o));
-  uint32_t c = 0, w = S.words[0][lane];
-  for (uint32_t t = 0; t < trips; ++t) {
-    while (w == 0u && c + 1u < nch) w = S.words[++c][lane];
-    if (w) {
-      const uint32_t j = 31u - __clz(w);
-      w ^= 1u << j;
-      const float4 it = S.P[c * 32u + j];
-      grp_force(it.x, it.y, it.z, np, ax, ay);
-    }
+  const uint32_t lanebit = 1u << lane;
+#pragma unroll 4
+  for (uint32_t i = 0; i < n; ++i) {
+    const float4 it = S.P[i];
+    if (__float_as_uint(it.w) & lanebit) grp_force(it.x, it.y, it.z, np, ax, ay);
   }
 }
 

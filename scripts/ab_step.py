@@ -24,11 +24,11 @@ ap.add_argument("--tree", default="quad", choices=["quad", "lbvh", "bvhref"])
 ap.add_argument("--theta", type=float, default=0.5)
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--reps", type=int, default=3)
-ap.add_argument("--dfs", action="store_true", help="NB_FORCE_FAST with the depth-first walk instead of the group walk")
+ap.add_argument("--group", action="store_true", help="NB_FORCE_FAST with the list-then-evaluate group walk instead of the depth-first walk")
 args = ap.parse_args()
 scene = {"disc": nb.NB_SCENE_UNIFORM_DISC, "plummer": nb.NB_SCENE_PLUMMER}[args.scene]
 tree = {"quad": nb.NB_TREE_QUAD, "lbvh": nb.NB_TREE_LBVH, "bvhref": nb.NB_TREE_BVH_REF}[args.tree]
-w = nb.World(args.n, theta=args.theta, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_FAST, fast_walk_dfs=args.dfs)
+w = nb.World(args.n, theta=args.theta, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_FAST, fast_walk_group=args.group)
 w.generate_on_device(scene, 1, args.n)
 cc = nb.Counting()
 ax, ay = w.accel(cc)
@@ -49,7 +49,7 @@ for _ in range(args.reps):
         best = r
 x, y, vx, vy, _ = w.get_soa()
 state = hashlib.sha256(x.tobytes() + y.tobytes() + vx.tobytes() + vy.tobytes()).hexdigest()[:16]
-print(json.dumps({"lib": os.environ.get("NB_B200_LIB", "in-tree"), "workload": f"{args.n} {args.scene} {args.tree} theta={args.theta}" + (" dfs" if args.dfs else ""),
+print(json.dumps({"lib": os.environ.get("NB_B200_LIB", "in-tree"), "workload": f"{args.n} {args.scene} {args.tree} theta={args.theta}" + (" group" if args.group else ""),
                   "interactions": int(cc.interactions), "accel_sha": digest, "state_sha": state,
                   **{k: round(v, 4) for k, v in best.items()}}))
 w.close()

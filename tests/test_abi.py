@@ -36,7 +36,7 @@ def test_abi_version_and_struct_sizes():
     assert C.sizeof(_lib.NbCounting) == 5 * 8 + 7 * 8
     assert C.sizeof(_lib.NbTreeInfo) == 4 * 8 + 2 * 4 + 3 * 4 + 5 * 4
     # fields carved out of the reserved words (ABI version unchanged: old callers passed / read zeros there)
-    assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.fast_walk_dfs.offset == 56 and _lib.NbConfig.reserved.offset == 60
+    assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.fast_walk_group.offset == 56 and _lib.NbConfig.reserved.offset == 60
     assert _lib.NbTreeInfo.sort_top_digits.offset == 52 and _lib.NbTreeInfo.sort_redone.offset == 56
     cfg = _lib.NbConfig()
     L.nb_default_config(C.byref(cfg), 10)
