@@ -712,9 +712,10 @@ __global__ void __launch_bounds__(256) bvh_sizes_kernel(BvhWork W) {
     if (!(W.nodes[v].flags & kBNodeLeaf)) continue;
     uint32_t p = W.nodes[v].parent;
     while (p != 0xffffffffu) {
-      // release: this child's size is visible before its arrival; the owner's ld.cg loads below are issued only
-      // after the atomic's result decided the branch (same protocol as tree_finish_kernel)
+      // release: this child's size is visible before its arrival; the owner acquires (same protocol as
+      // tree_finish_kernel)
       if (atomic_add_release(&W.nodes[p].arrive, 1u) == 0u) break; // the second child to arrive owns the parent
+      fence_acquire_gpu();
       const uint32_t c0 = W.nodes[p].child0;
       const uint32_t sz = 1u + __ldcg(&W.nodes[c0].size) + __ldcg(&W.nodes[c0 + 1].size);
       W.nodes[p].size = sz;

@@ -153,14 +153,15 @@ __global__ void peer_wait_kernel(const uint32_t *my_flags, int n_ranks, uint32_t
   }
 }
 
+// id_from_pad: the record's pad word holds the body's original index (slot-order snapshots of NB_TREE_BVH_REF)
 __global__ void __launch_bounds__(256) aos_to_soa_kernel(const float *__restrict__ aos /*6 words per body*/,
-                                                         BodyArrays b, uint32_t n) {
+                                                         BodyArrays b, uint32_t n, bool id_from_pad = false) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float2 p = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i);
   const float2 v = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i + 2);
   const uint2 w = *reinterpret_cast<const uint2 *>(aos + 6 * (size_t)i + 4);
-  b.x[i] = p.x; b.y[i] = p.y; b.vx[i] = v.x; b.vy[i] = v.y; b.m[i] = w.x; b.id[i] = i;
+  b.x[i] = p.x; b.y[i] = p.y; b.vx[i] = v.x; b.vy[i] = v.y; b.m[i] = w.x; b.id[i] = id_from_pad ? w.y : i;
 }
 
 // Slot order -> ORIGINAL body order AoS.
@@ -210,13 +211,14 @@ __global__ void __launch_bounds__(256) scene_kernel(int scene, unsigned long lon
 }
 
 // Slot order -> AoS in the SAME order: what the reference's Vec looks like after BVHTree::from permuted it.
-__global__ void __launch_bounds__(256) soa_to_aos_slot_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos) {
+__global__ void __launch_bounds__(256) soa_to_aos_slot_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos,
+                                                              bool id_in_pad = false) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   const size_t o = 6 * (size_t)s;
   *reinterpret_cast<float2 *>(aos + o) = make_float2(b.x[s], b.y[s]);
   *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(b.vx[s], b.vy[s]);
-  *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
+  *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], id_in_pad ? b.id[s] : 0u);
 }
 
 __global__ void __launch_bounds__(256) set_identity_kernel(uint32_t *id, uint32_t n) {
@@ -279,14 +281,16 @@ struct DrawScratch {
   uint32_t *heavy;  // max original id + 1 of a heavy body on the pixel
 };
 
+// by_slot (NB_TREE_BVH_REF): the reference draws its Vec in the order BVHTree::from left it (main.rs:46, :400), i.e.
+// slot order, so "last" is the largest SLOT; otherwise the Vec order is the original body order.
 __global__ void __launch_bounds__(256) draw_splat_kernel(BodyArrays b, uint32_t n, uint32_t render_h, float world_h,
-                                                         uint32_t cell, DrawScratch d) {
+                                                         uint32_t cell, DrawScratch d, bool by_slot) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   const float px = b.x[s], py = b.y[s];
   if (!(py < world_h && px < world_h && py >= 0.f && px >= 0.f)) return; // within_bounds, main.rs:223-226
   const uint32_t pix = ((uint32_t)py / cell) * render_h + ((uint32_t)px / cell);
-  const uint32_t oid = b.id[s] + 1u;
+  const uint32_t oid = (by_slot ? s : b.id[s]) + 1u;
   if (b.m[s] > 10u) atomicMax(&d.heavy[pix], oid);
   else {
     atomicAdd(&d.hits[pix], 1u);

@@ -250,6 +250,9 @@ int enqueue_build(nb_ctx *c) {
   cudaStream_t st = c->stream;
   BodyArrays &b = c->body[c->cur];
   if (n == 0) return NB_OK;
+  // a failed build is not sticky: every build starts with a clean error word (the failed step itself left the
+  // state untouched, see copy_body in integrate.cuh)
+  NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), st));
   if (c->bvh_ref) return enqueue_build_bvh_ref(c);
   if (!c->quad && c->cfg.domain_auto) {
     const int np = kSMs * 4;
@@ -384,7 +387,10 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
     float *arrs[4] = {out.x, out.y, out.vx, out.vy};
     for (float *a : arrs) {
       r = g_nccl.AllGather(a + per * (size_t)c->rank, a, per, ncclFloat32, c->comm, c->stream);
-      if (r != ncclSuccess) return nccl_fail(c, r, "ncclAllGather");
+      if (r != ncclSuccess) {
+        g_nccl.GroupEnd(); // do not leave the group open behind the error
+        return nccl_fail(c, r, "ncclAllGather");
+      }
     }
     if ((r = g_nccl.GroupEnd()) != ncclSuccess) return nccl_fail(c, r, "ncclGroupEnd");
   } else if (ev_after_integrate) {
@@ -493,7 +499,7 @@ __global__ void draw_compose_kernel(DrawScratch d, const uint32_t *__restrict__ 
   if (d.heavy[p]) {
     px = make_uchar4(0x00, 0xff, 0x00, 0xff); // main.rs:55-59
   } else if (d.hits[p]) {
-    const uint32_t s = slot_of[d.last[p] - 1u];
+    const uint32_t s = slot_of ? slot_of[d.last[p] - 1u] : d.last[p] - 1u; // null: `last` is a slot already
     // main.rs:61-63: 0x10 + (((|vx|+|vy|)*10.0) as u8).min(0xef); `as u8` saturates, NaN -> 0
     const float sp = __fmul_rn(__fadd_rn(fabsf(b.vx[s]), fabsf(b.vy[s])), 10.0f);
     uint32_t q = (sp != sp) ? 0u : (sp <= 0.f ? 0u : (sp >= 255.f ? 255u : (uint32_t)sp));
@@ -1048,9 +1054,9 @@ int nb_draw(nb_ctx *c, uint8_t *frame, uint32_t render_h) {
   BodyArrays &b = c->body[c->cur];
   if (n) {
     slot_of_id_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b.id, n, slot_of);
-    draw_splat_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b, n, render_h, (float)world_h, cell, d);
+    draw_splat_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b, n, render_h, (float)world_h, cell, d, c->bvh_ref);
   }
-  draw_compose_kernel<<<cdiv(npix, 256), 256, 0, c->stream>>>(d, slot_of, b, npix, dframe);
+  draw_compose_kernel<<<cdiv(npix, 256), 256, 0, c->stream>>>(d, c->bvh_ref ? nullptr : slot_of, b, npix, dframe);
   NB_CUDA(c, cudaGetLastError());
   NB_CUDA(c, cudaMemcpyAsync(frame, dframe, 4 * (size_t)npix, cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1062,12 +1068,22 @@ int nb_draw(nb_ctx *c, uint8_t *frame, uint32_t render_h) {
 int nb_save_snapshot(nb_ctx *c, const char *path, uint64_t steps_done) {
   if (!c || !path) return NB_ERR_INVALID;
   std::vector<nb_particle> buf(c->n);
-  int rc = nb_get_bodies_aos(c, buf.data(), buf.size());
+  int rc = NB_OK;
+  if (c->bvh_ref && c->n) {
+    // BVHTree::from starts from the Vec order the previous build left (the partition swaps in place and the f32
+    // sums are sequential): the snapshot keeps the SLOT order, with the original index of each body in the pad word
+    NB_CUDA(c, cudaSetDevice(c->device));
+    soa_to_aos_slot_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos, true);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(buf.data(), c->aos, (size_t)c->n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  } else
+    rc = nb_get_bodies_aos(c, buf.data(), buf.size());
   if (rc != NB_OK) return rc;
   FILE *f = fopen(path, "wb");
   if (!f) return fail(c, NB_ERR_INVALID, std::string("cannot open ") + path);
   const char magic[8] = {'N', 'B', 'B', '2', 'S', 'N', 'A', 'P'};
-  const uint32_t ver[2] = {1u, 0u};
+  const uint32_t ver[2] = {2u, c->bvh_ref ? 1u : 0u}; // flags bit 0: slot order, pad = original index
   const uint64_t hdr[2] = {(uint64_t)c->n, steps_done};
   bool ok = fwrite(magic, 1, 8, f) == 8 && fwrite(ver, 4, 2, f) == 2 && fwrite(hdr, 8, 2, f) == 2 &&
             fwrite(buf.data(), sizeof(nb_particle), buf.size(), f) == buf.size();
@@ -1083,7 +1099,7 @@ int nb_load_snapshot(nb_ctx *c, const char *path, uint64_t *steps_done) {
   uint32_t ver[2];
   uint64_t hdr[2];
   bool ok = fread(magic, 1, 8, f) == 8 && fread(ver, 4, 2, f) == 2 && fread(hdr, 8, 2, f) == 2 &&
-            std::memcmp(magic, "NBB2SNAP", 8) == 0 && ver[0] == 1u;
+            std::memcmp(magic, "NBB2SNAP", 8) == 0 && (ver[0] == 1u || ver[0] == 2u);
   if (!ok) { fclose(f); return fail(c, NB_ERR_INVALID, std::string("not a snapshot: ") + path); }
   if (hdr[0] > c->cfg.n_max) { fclose(f); return fail(c, NB_ERR_CAPACITY, "snapshot holds more bodies than n_max"); }
   std::vector<nb_particle> buf(hdr[0]);
@@ -1091,7 +1107,13 @@ int nb_load_snapshot(nb_ctx *c, const char *path, uint64_t *steps_done) {
   fclose(f);
   if (!ok) return fail(c, NB_ERR_INVALID, std::string("truncated snapshot: ") + path);
   if (steps_done) *steps_done = hdr[1];
-  return nb_set_bodies_aos(c, buf.data(), buf.size());
+  int rc = nb_set_bodies_aos(c, buf.data(), buf.size());
+  if (rc == NB_OK && ver[0] == 2u && (ver[1] & 1u) && !buf.empty()) { // slot-order snapshot: ids from the pad words
+    aos_to_soa_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], c->n, true);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return rc;
 }
 
 // ---- multi-GPU -------------------------------------------------------------------------------

@@ -374,6 +374,11 @@ __device__ __forceinline__ uint32_t atomic_add_release(uint32_t *p, uint32_t v) 
   asm volatile("atom.add.release.gpu.global.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
   return old;
 }
+// Acquire side of the hand-off, paid only by the thread that completes a parent: the releasing arrivals of the
+// other children synchronise with this fence through the arrival counter (PTX memory model: release pattern on
+// the atomic, fence.acq_rel after the read-modify-write that observed them), so the children's summaries read
+// next are the ones written before those arrivals.
+__device__ __forceinline__ void fence_acquire_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
 template <bool LBVH> struct LeafAcc {
   float ax = 0.f, ay = 0.f;
@@ -555,8 +560,7 @@ __global__ void __launch_bounds__(128, 12) tree_finish_kernel(Meta *__restrict__
       const uint32_t old = atomic_add_release(&T.arrive[parent], REF ? 1u : cur_count);
       const uint32_t total = lp.z & kCountMask;
       if (REF ? (old != 1u) : (old + cur_count != total)) break;
-      // acquire side: the children's summaries are read with ld.cg (L2, the coherence point) by loads that are
-      // issued only after the atomic's result decided the branch above — no second fence
+      fence_acquire_gpu(); // the children's summaries below were written before the arrivals this atomic observed
       uint32_t pm = 0;
       float bx = 0.f, by = 0.f;
       bool first = true;

@@ -187,3 +187,54 @@ def test_bvh_ref_faithful_index_bug_matches_the_reference_as_shipped():
     assert not np.array_equal(bits(ref.particles["vx"]), bits(q["vx"]))
     w.close()
     ref.close()
+
+
+def test_bvh_ref_snapshot_resume_is_bit_identical(tmp_path):
+    # BVHTree::from depends on the Vec order the previous build left: the snapshot keeps slot order + ids (version 2)
+    p = scene("galaxy", 30_000)
+    a = nb.World(len(p), theta=0.7, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    a.set_particles(p)
+    a.step(3)
+    a.save(tmp_path / "s.nbb", 3)
+    a.step(2)
+    b = nb.World(len(p), theta=0.7, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    assert b.load(tmp_path / "s.nbb") == 3
+    b.step(2)
+    assert np.array_equal(bits(a.particles), bits(b.particles))  # by original id
+    ha, hb = a.particles.copy(), b.particles.copy()
+    a.close()
+    b.close()
+    assert np.array_equal(bits(ha), bits(hb))
+
+
+def draw_sequential(p, H=100000, R=1250):
+    """Sequential restatement of draw() (src/main.rs:41-72) over the Vec order given."""
+    ref = np.zeros((R * R, 4), np.uint8)
+    for q in p:
+        x, y = q["x"], q["y"]
+        if not (y < H and x < H and y >= 0 and x >= 0):
+            continue
+        off = (int(y) // (H // R)) * R + (int(x) // (H // R))
+        if q["weight"] > 10:
+            ref[off] = (0, 0xFF, 0, 0xFF)
+        elif ref[off, 3] != 0xFF:
+            sp = (abs(np.float32(q["vx"])) + abs(np.float32(q["vy"]))) * np.float32(10.0)
+            v = 0 if np.isnan(sp) else int(min(max(sp, 0), 255))
+            vel = 0x10 + min(v, 0xEF)
+            a = int(ref[off, 3])
+            ref[off] = (0xFF, 0xFF - vel, 0xFF - vel, a + 10 if a <= 240 else a)
+    return ref
+
+
+def test_bvh_ref_draw_follows_the_permuted_vec_order():
+    # after BVHTree::from the reference draws its Vec in the post-partition order (main.rs:46 after :400): pixels hit
+    # by several light bodies take the colour of the last one IN THAT ORDER
+    p = scene("disc", 120_000)
+    p["vx"] = (np.arange(len(p)) % 23).astype(np.float32) * 0.5  # distinct colours per body
+    w = nb.World(len(p), theta=50.0, dt=0.1, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    host = p.copy()
+    w.update_host(host, 0.0)  # delta 0: positions and velocities stay, the Vec comes back permuted
+    assert not np.array_equal(bits(host["x"]), bits(p["x"]))
+    frame = w.draw().reshape(-1, 4)
+    assert np.array_equal(frame, draw_sequential(host))
+    w.close()
