@@ -232,6 +232,13 @@ class World:
         self._ck(self._L.nb_scene_generate_device(self._ctx, int(scene), int(seed), int(n)))
         self.n = int(n)
 
+    def profile_step(self):
+        """One step with an event behind every kernel: [(name, microseconds), ...] in launch order."""
+        buf = (_lib.NbKernelTime * 64)()
+        k = C.c_size_t()
+        self._ck(self._L.nb_profile_step(self._ctx, buf, 64, C.byref(k)))
+        return [(buf[i].name.decode(), float(buf[i].us)) for i in range(k.value)]
+
     def draw(self, render_h=RENDER_HEIGHT):
         """`draw(particles, frame)` (src/main.rs:41-72) into a headless RGBA8 frame."""
         frame = np.zeros((render_h, render_h, 4), np.uint8)

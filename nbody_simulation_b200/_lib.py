@@ -45,6 +45,10 @@ class NbConfig(C.Structure):
     ]
 
 
+class NbKernelTime(C.Structure):
+    _fields_ = [("name", C.c_char * 56), ("us", C.c_double)]
+
+
 class NbCounting(C.Structure):
     _fields_ = [
         ("build_s", C.c_double),
@@ -145,6 +149,7 @@ def load(path=LIB_PATH):
         "nb_get_tree_info": (C.c_int, [vp, P(NbTreeInfo)]),
         "nb_get_tree": (C.c_int, [vp, P(NbTreeView)]),
         "nb_draw": (C.c_int, [vp, vp, C.c_uint32]),
+        "nb_profile_step": (C.c_int, [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
         "nb_save_snapshot": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
         "nb_load_snapshot": (C.c_int, [vp, C.c_char_p, P(C.c_uint64)]),
         "nb_comm_unique_id": (C.c_int, [vp]),

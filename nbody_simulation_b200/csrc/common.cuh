@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <vector>
 
 namespace nb {
 
@@ -9,6 +10,17 @@ constexpr int kSMs = 148;                 // B200
 
 // Kernel launches issued by this library on the calling thread (reported in nb_counting).
 static thread_local unsigned long long g_launches = 0;
+// nb_profile_step: while g_prof points at a list, every host-side launch site drops a named event behind its
+// kernel(s); the differences between consecutive events are the kernels' durations in stream order.
+struct ProfMark { const char *name; cudaEvent_t ev; };
+static thread_local std::vector<ProfMark> *g_prof = nullptr;
+inline void prof_mark(cudaStream_t st, const char *name) {
+  if (!g_prof) return;
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, st);
+  g_prof->push_back({name, e});
+}
 constexpr int kKeyBits = 48;              // 24 quadtree levels x 2 bits (y bit above x bit)
 constexpr int kQuadLevels = 24;
 constexpr unsigned long long kKeyOut = 1ull << 48; // body outside the root square (quadtree mode)

@@ -262,6 +262,7 @@ int enqueue_build(nb_ctx *c) {
   }
   g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
   morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
+  prof_mark(st, "morton_kernel");
   // Quadtree: sort only as many top digits as the previous build's depth (+1 level) needs; tree_count_kernel
   // verifies, and the conditional passes behind it redo the sort in full if the guess was too shallow
   // (radix_sort.cuh).  Digit p from the top covers 4 quadtree levels (the top digit also holds the outside bit).
@@ -282,13 +283,16 @@ int enqueue_build(nb_ctx *c) {
   if (c->quad)
     tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
+  prof_mark(st, "tree_count_kernel");
   scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, c->meta);
+  prof_mark(st, "scan_bsum_kernel");
   if (top_passes) {
     const uint32_t *cond = &c->meta->resort;
     radix_sort_fallback(c->keys[0], c->vals[0], c->keys[1], c->vals[1], which, n, 49, top_passes, c->sort, st, cond);
     tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 0, cond);
     scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, nullptr, cond);
     g_launches += 2;
+    prof_mark(st, "fallback chain (no-ops unless the depth guess failed)");
   }
   // Parent / children / twig links: from the parents' side, either inside the emit kernel (extra searches on the
   // ~30 % of lanes that hold internal nodes) or by tree_link_kernel (chases skip links).  Measured build phase,
@@ -298,16 +302,19 @@ int enqueue_build(nb_ctx *c) {
   if (c->quad && emit_links) tree_emit_quad_kernel<true><<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   else if (c->quad) tree_emit_quad_kernel<false><<<cdiv(n, (uint32_t)kEmitBodies), 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
   else tree_emit_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leafdepth, c->nstart, bbase, c->T);
+  prof_mark(st, "tree_emit_kernel");
   const uint32_t link_blocks = std::max((uint32_t)kSMs * 8u, cdiv(n / 2u, 256u));
   if (!c->quad || !emit_links) g_launches += 1;
   if (!c->quad) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
   else if (!emit_links) tree_link_kernel<true><<<link_blocks, 256, 0, st>>>(c->meta, c->T);
+  if (!c->quad || !emit_links) prof_mark(st, "tree_link_kernel");
   // about one node per thread (the grid-stride loop covers the rest): a thread that completes a parent climbs on
   // while its warp-mates idle, so short-lived warps keep the machine full where a long loop would serialise tails
   const uint32_t fin_blocks = std::max((uint32_t)kSMs * 16u, cdiv(n / 2u, 128u)); // measured: 0.38 -> 0.36 ms build at 1M, 2.32 -> 1.91 at 8M
   if (c->quad) tree_finish_kernel<false, 8><<<fin_blocks, 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
   else // one warp per node: about n / 16 warps (an LBVH of 64-body buckets has ~n / 20 nodes)
     tree_finish_kernel<true, 8, false, true><<<std::max((uint32_t)kSMs * 16u, cdiv(n / 16u, 4u)), 128, 0, st>>>(c->meta, c->T, order, b.x, b.y, b.m, b.id, c->sbody);
+  prof_mark(st, "tree_finish_kernel");
   NB_CUDA(c, cudaGetLastError());
   c->tree_valid = true;
   return NB_OK;
@@ -342,6 +349,7 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   else NB_TRAVERSE_FAST(false);
 #undef NB_TRAVERSE
 #undef NB_TRAVERSE_FAST
+  prof_mark(c->stream, "traverse");
   NB_CUDA(c, cudaGetLastError());
   return NB_OK;
 }
@@ -396,6 +404,7 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   } else if (ev_after_integrate) {
     NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
   }
+  prof_mark(c->stream, c->n_ranks > 1 ? "integrate + exchange" : "integrate_resort_kernel");
   NB_CUDA(c, cudaGetLastError());
   c->cur ^= 1;
   c->tree_valid = false;
@@ -834,6 +843,30 @@ int nb_step(nb_ctx *c, uint32_t n_steps, nb_counting *out) {
   if (!c) return NB_ERR_INVALID;
   NB_CUDA(c, cudaSetDevice(c->device));
   return do_steps(c, n_steps, c->cfg.dt, out);
+}
+
+int nb_profile_step(nb_ctx *c, nb_kernel_time *out, size_t cap, size_t *count) {
+  if (!c || !out || !count) return NB_ERR_INVALID;
+  NB_CUDA(c, cudaSetDevice(c->device));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  std::vector<ProfMark> marks;
+  g_prof = &marks;
+  prof_mark(c->stream, "start");
+  const int rc = do_steps(c, 1, c->cfg.dt, nullptr);
+  g_prof = nullptr;
+  size_t k = 0;
+  for (size_t i = 1; i < marks.size(); ++i) {
+    float ms = 0.f;
+    if (rc == NB_OK && k < cap && cudaEventElapsedTime(&ms, marks[i - 1].ev, marks[i].ev) == cudaSuccess) {
+      std::memset(&out[k], 0, sizeof(out[k]));
+      std::strncpy(out[k].name, marks[i].name, sizeof(out[k].name) - 1);
+      out[k].us = (double)ms * 1e3;
+      ++k;
+    }
+  }
+  for (ProfMark &m : marks) cudaEventDestroy(m.ev);
+  *count = k;
+  return rc;
 }
 
 int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_counting *out) {

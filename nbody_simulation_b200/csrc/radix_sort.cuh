@@ -302,6 +302,7 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
   g_launches += 2 + (plan.passes - first);
   sort_histogram_kernel<<<hblocks, 256, plan.hist_total * sizeof(uint32_t), st>>>(keys_a, n, plan, sc.ghist);
   sort_scan_hist_kernel<<<plan.passes, 512, 0, st>>>(sc.ghist, plan, sc.tickets, meta, n);
+  prof_mark(st, "sort_histogram_kernel");
   unsigned long long *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
   int which = 0;
@@ -313,6 +314,7 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
     unsigned long long *tk = kin; kin = kout; kout = tk;
     uint32_t *tv = vin; vin = vout; vout = tv;
     which ^= 1;
+    prof_mark(st, "sort_onesweep_kernel");
   }
   return which;
 }

@@ -1039,6 +1039,38 @@ int orc_world_update(void *h, int kind, float delta, float theta, float x0, floa
         }
       }
     }
+  } else if (kind == 2) {
+    // literal quad_tree.rs, timed as the reference would run it: QuadTree::new, insert every in-bounds body
+    // (within_bounds, main.rs:223-226), calculate_gravity.  No Morton keys, no flattening: the reference's
+    // insert computes neither, and the recursive walk below needs neither.
+    if (dh <= 0.f) { x0 = 0.f; y0 = 0.f; dh = 100000.f; }
+    QuadArena A;
+    Quad *root = A.make(RectQ::make(V2{x0, y0}, dh));
+    for (size_t i = 0; i < n; ++i) {
+      const Particle &q = cloned[i];
+      if (in_domain(q.position.x, q.position.y, x0, y0, dh))
+        quad_insert(A, root, SmallParticle{q.position, q.weight, (uint32_t)i}, 0);
+    }
+    quad_calculate_gravity(root);
+    t1 = now_s();
+#pragma omp parallel for schedule(dynamic, 5000) num_threads(threads) reduction(+ : ti, tt)
+    for (long long i = 0; i < (long long)n; i += (long long)sample_stride) {
+      V2 acc{0.f, 0.f};
+      Counters c;
+      quad_sum_gravity(cloned[i].position, root, acc, theta, c);
+      acceleration[i] = acc;
+      ti += c.interactions;
+      tt += c.tests;
+    }
+    t2 = now_s();
+    if (sample_stride == 1) {
+      for (size_t idx = 0; idx < n; ++idx) {
+        Particle &p = W->particles[idx];
+        p.velocity = p.velocity + acceleration[idx] * delta;
+        V2 velo = p.velocity * delta;
+        p.position = p.position + velo;
+      }
+    }
   } else {
     std::vector<float> x(n), y(n);
     std::vector<uint32_t> w(n);

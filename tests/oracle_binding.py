@@ -8,8 +8,14 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_SO = os.path.join(ORACLE_DIR, "_build", "libnbody_oracle.so")
+NATIVE_SO = os.path.join(ORACLE_DIR, "_build", "libnbody_oracle_native.so")
+NATIVE_FLAGS = "-O3 -march=native -ffp-contract=off -fno-fast-math -fopenmp -fPIC -std=c++17 -Wall -Wno-unknown-pragmas"
+PORTABLE_FLAGS = "-O3 -march=x86-64-v3 -ffp-contract=off -fno-fast-math -fopenmp -fPIC -std=c++17"
+build_flags = PORTABLE_FLAGS  # of the library lib() loaded
 
-from nbody_simulation_b200._lib import NbCounting, NbTreeInfo, NbTreeView, alloc_tree_view  # struct layouts
+# struct layouts only: importing the package does not load libnbody_b200.so (that happens on the first call)
+from nbody_simulation_b200._lib import (PARTICLE_DTYPE, NbCounting, NbTreeInfo, NbTreeView,  # noqa: E402
+                                        alloc_tree_view)
 
 KIND_PIPE_QUAD, KIND_PIPE_LBVH, KIND_LITERAL_QUAD, KIND_LITERAL_BVH = 0, 1, 2, 3
 
@@ -21,8 +27,19 @@ def lib():
     if _lib is not None:
         return _lib
     # `make` is a no-op when the library is newer than its source and the shared header
-    subprocess.check_call(["make", "-C", ORACLE_DIR], stdout=subprocess.DEVNULL)
-    L = C.CDLL(ORACLE_SO)
+    global build_flags
+    so = ORACLE_SO
+    if os.environ.get("NB_ORACLE_NATIVE") == "1":
+        # timed CPU baseline: built on THIS machine for its own cores (-O3 -march=native)
+        try:
+            subprocess.check_call(["make", "-C", ORACLE_DIR, f"OUT={NATIVE_SO}", f"CXXFLAGS={NATIVE_FLAGS}"],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=300)
+            so, build_flags = NATIVE_SO, NATIVE_FLAGS
+        except Exception:
+            so = ORACLE_SO
+    if so == ORACLE_SO:
+        subprocess.check_call(["make", "-C", ORACLE_DIR], stdout=subprocess.DEVNULL)
+    L = C.CDLL(so)
     vp, f, P = C.c_void_p, C.c_float, C.POINTER
     L.orc_pair_force.argtypes = [f, f, f, f, f, P(f), P(f)]
     L.orc_pair_force.restype = None
@@ -51,8 +68,20 @@ def lib():
     L.orc_world_get.restype = None
     L.orc_world_update.argtypes = [vp, C.c_int, f, f, f, f, f, C.c_int, C.c_int, C.c_int, C.c_size_t, P(NbCounting)]
     L.orc_num_threads.restype = C.c_int
+    L.nb_scene_generate.argtypes = [C.c_int32, C.c_uint64, C.c_size_t, vp, C.c_size_t]
+    L.nb_scene_generate.restype = C.c_size_t
     _lib = L
     return L
+
+
+def generate_scene(scene, seed=1, n=0):
+    """The seeded scenes of csrc/scene.cpp as compiled into the ORACLE library (same source file, same bits as
+    nbody_simulation_b200.generate_scene): inputs for the reference arm without loading the product library."""
+    L = lib()
+    total = L.nb_scene_generate(scene, seed, n, None, 0)
+    out = np.zeros(total, dtype=PARTICLE_DTYPE)
+    assert L.nb_scene_generate(scene, seed, n, out.ctypes.data, total) == total
+    return out
 
 
 def _f32(a):
