@@ -45,10 +45,34 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
+    ap.add_argument("--config", type=int, default=0, choices=[0, 1, 2, 3, 4, 5],
+                    help="BASELINE.json configs[N-1] (BASELINE.md §2 table): sets scene / bodies / tree / theta; "
+                         "0 = the default line (config 2 weak-scaled).  1: default scene (CPU path of the reference: use "
+                         "--impl reference; ours runs its own tree for comparison); 3: 4M Plummer, LBVH; "
+                         "4: 16M two-galaxy over --gpus ranks (strong-scaled); 5: 64M Plummer over --gpus ranks")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the bit-identity check against one GPU")
     ap.add_argument("--full-sort", action="store_true",
                     help="quadtree: sort every key digit in every build (default: only the digits the tree depth needs, "
                          "checked on the device each step; same tree either way)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    args.total_bodies = None  # None: weak scaling, n_per_gpu x world
+    if args.config == 1:
+        args.scene, args.total_bodies = "default", 0
+        if args.tree == "quad" and "--tree" not in sys.argv:
+            args.tree = "bvhref"  # the reference's live tree (bvh_tree.rs)
+        if "--theta" not in sys.argv:
+            args.theta = 50.0     # THETA as shipped (main.rs:35); pass --theta 0.5 for the other half of config 1
+    elif args.config == 3:
+        args.scene, args.tree, args.total_bodies = "plummer", ("lbvh" if "--tree" not in sys.argv else args.tree), 4_000_000
+    elif args.config == 4:
+        args.scene, args.total_bodies = "galaxy", 16_000_000
+    elif args.config == 5:
+        args.scene, args.total_bodies = "plummer", 64_000_000
+    return args
+
+
+def total_bodies(args, world):
+    return args.n_per_gpu * world if args.total_bodies is None else args.total_bodies
 
 
 def make_scene(nb, args, n_total):
@@ -58,8 +82,16 @@ def make_scene(nb, args, n_total):
 
 
 def workload_name(args, n_total):
-    return (f"{n_total}-body {args.scene} scene, {args.tree} tree, theta={args.theta}, dt=0.1 "
-            f"(BASELINE.json configs[1] scaled weakly: {args.n_per_gpu} bodies per GPU)")
+    which = {0: f"BASELINE.json configs[1] scaled weakly: {args.n_per_gpu} bodies per GPU", 1: "BASELINE.json configs[0]",
+             2: "BASELINE.json configs[1]", 3: "BASELINE.json configs[2]", 4: "BASELINE.json configs[3], strong-scaled",
+             5: "BASELINE.json configs[4], strong-scaled"}[args.config]
+    return f"{n_total}-body {args.scene} scene, {args.tree} tree, theta={args.theta}, dt=0.1 ({which})"
+
+
+def workload_config(args, n_total):
+    """The `config` object: names the workload only, identical in both arms (ours / --impl reference)."""
+    return {"workload": workload_name(args, n_total), "n_bodies": n_total, "scene": args.scene, "theta": args.theta,
+            "tree": args.tree, "dt": 0.1}
 
 
 class ClockSampler:
@@ -129,12 +161,42 @@ def measured_peaks():
         return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
 
 
+def hbm_rooflines(kernel_times, n, n_nodes, hbm_gbs, peak_src):
+    """Achieved HBM GB/s of the step's memory-bound kernels: ALGORITHMIC bytes (SURVEY.md §8 d) over the
+    device time nb_profile_step measured for each (one step, events behind every kernel, L2 flushed before)."""
+    per_body = {  # bytes per body
+        "morton_kernel": 20.0,          # x, y read (8) + key (8) + slot index (4) written
+        "sort_histogram_kernel": 8.0,   # one read of the keys, all digits
+        "sort_onesweep_kernel": 24.0,   # (key, slot) read + written
+        "tree_count_kernel": 13.0,      # key read (8) + leaf depth (1) + node-count prefix (4) written
+        "integrate_resort_kernel": 60.0,  # order 4 + acc 8 + 24 gathered + 24 written
+    }
+    per_node = {"tree_emit_kernel": 84.0, "tree_link_kernel": 56.0}  # node records written / linked
+    out, seen = [], {}
+    for name, us in kernel_times:
+        if name in per_body:
+            b = per_body[name] * n
+        elif name in per_node:
+            b = per_node[name] * n_nodes
+        elif name == "tree_finish_kernel":
+            b = 40.0 * n + 100.0 * n_nodes  # leaf fix-up + gather per body; summaries read / written per node
+        else:
+            continue
+        k = seen.get(name, 0)
+        seen[name] = k + 1
+        gbs = b / (us * 1e-6) / 1e9 if us > 0 else 0.0
+        out.append({"kernel": name + (f" #{k + 1}" if name == "sort_onesweep_kernel" else ""), "bytes": b, "us": us,
+                    "achieved_gbs": gbs, "frac": gbs / hbm_gbs})
+    return {"peak_gbs": hbm_gbs, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_src})", "kernels": out,
+            "all_kernels_us": [[nm, round(us, 2)] for nm, us in kernel_times]}
+
+
 def cpu_port_steps(parts, args, n_steps, warmup, stride, threads=0):
     """The reference's CPU path (oracle port of quad_tree.rs / bvh_tree.rs + main.rs:388-425) on the host
     cores.  stride > 1: the traversal covers every stride-th body (rayon's per-body independence makes
     the sample exact for throughput); build and integrate are always full."""
     import oracle_binding as ob
-    from nbody_simulation_b200._lib import NbCounting
+    from nbody_simulation_b200._lib import NbCounting  # struct layout only; does not load libnbody_b200.so
 
     kind = ob.KIND_LITERAL_QUAD if args.tree == "quad" else ob.KIND_LITERAL_BVH
     if threads <= 0:  # all usable host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
@@ -160,27 +222,39 @@ def cpu_port_steps(parts, args, n_steps, warmup, stride, threads=0):
 
 
 def run_reference(args, rank, world):
+    """The reference's CPU implementation of the path (oracle port; the reference is Rust and cannot be built here)
+    on the host cores of this box: every body walked, every step timed; nothing of the product library is loaded."""
     if rank != 0:
         return
-    import nbody_simulation_b200 as nb
+    os.environ.setdefault("NB_ORACLE_NATIVE", "1")  # build the oracle for THIS box's cores (BASELINE.md §2)
+    import oracle_binding as ob
 
-    n_total = args.n_per_gpu * world
-    parts = make_scene(nb, args, n_total)
+    kinds = {"disc": 1, "plummer": 2, "galaxy": 3, "default": 0}  # NB_SCENE_* of include/nbody_b200.h
+    n_total = total_bodies(args, world)
+    parts = ob.generate_scene(kinds[args.scene], 1, n_total)
     n_total = len(parts)
-    stride = max(1, world)
-    r = cpu_port_steps(parts, args, args.steps, min(args.warmup, 1), stride)
-    sample = (f"{args.steps} World::update steps of the oracle port (literal "
+    warm = max(3, args.warmup)
+    # bound the run (~4 min): time one step, then run as many of the requested steps as fit; print what was run
+    t0 = time.perf_counter()
+    probe = cpu_port_steps(parts, args, 1, 0, 1)
+    t_step = max(time.perf_counter() - t0, 1e-3)
+    budget = 240.0
+    warm_run = min(warm, max(0, int(0.2 * budget / t_step)))
+    steps_run = max(1, min(args.steps, int((budget - (1 + warm_run) * t_step) / t_step)))
+    r = cpu_port_steps(parts, args, steps_run, warm_run, 1)
+    sample = (f"{steps_run} full World::update steps (every body walked) of the oracle port (literal "
               f"{'quad_tree.rs + carried-over traversal' if args.tree == 'quad' else 'bvh_tree.rs'}) on {n_total} "
-              f"bodies; build single-threaded, traversal OpenMP dynamic,5000 over every {stride}-th body"
-              + (" (scaled by the stride)" if stride > 1 else ""))
+              f"bodies; build single-threaded, traversal OpenMP dynamic,5000 on {r['cores']} threads; "
+              f"g++ {ob.build_flags}")
     line = {
         "impl": "reference", "metric": "barnes_hut_body_interactions_per_s", "value": r["value"],
-        "unit": "interactions/s", "n_gpus": world, "steps": args.steps, "warmup": min(args.warmup, 1),
-        "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
+        "unit": "interactions/s", "n_gpus": world, "steps": steps_run, "steps_requested": args.steps, "warmup": warm,
+        "warmup_run": warm_run,
+        "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak" if args.total_bodies is None else "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args, n_total), "n_bodies": n_total, "theta": args.theta,
-                   "tree": args.tree},
+        "config": workload_config(args, n_total),
         "steps_per_s": 1.0 / r["seconds_per_step"] if r["seconds_per_step"] > 0 else 0.0,
+        "interactions_per_step": r["interactions_per_step"],
         "cpu_baseline": {"value": r["value"], "unit": "interactions/s", "cores": r["cores"], "kind": "port",
                          "sample": sample},
         "e2e": {"value": r["value"], "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -225,7 +299,7 @@ def main():
         dist.all_reduce(t, op=op)
         return float(t.item())
 
-    n_total = args.n_per_gpu * world
+    n_total = total_bodies(args, world)
     parts = make_scene(nb, args, n_total)
     n_total = len(parts)
     tree = {"quad": nb.NB_TREE_QUAD, "lbvh": nb.NB_TREE_LBVH, "bvhref": nb.NB_TREE_BVH_REF}[args.tree]
@@ -299,29 +373,98 @@ def main():
     # ---- end to end through the host-buffer drop-in call ----------------------------------------------
     e2e = None
     if not args.no_e2e:
-        host, owner = nb.pinned_particles(n_total)
-        host[:] = parts
+        # N = 1: nb_world_update with the whole Vec.  N > 1: the Vec is sharded over the ranks' hosts
+        # (nb_world_update_shard): each rank uploads and downloads only ITS 1/N slice, the slices travel between the
+        # GPUs over NVLink.  Either way every body crosses PCIe once per direction per step.
+        sharded = world > 1 and args.exchange == "peer" and args.tree != "bvhref"
+        if sharded:
+            lo, hi = rank * n_total // world, (rank + 1) * n_total // world
+        else:
+            lo, hi = 0, n_total
+        host, owner = nb.pinned_particles(hi - lo)
+
+        def e2e_step(counter=None):
+            if sharded:
+                w.update_host_shard(host, lo, n_total, 0.1, counter)
+            else:
+                w.update_host(host, 0.1, counter)
+
+        host[:] = parts[lo:hi]
         for _ in range(2):
-            w.update_host(host, 0.1)
-        host[:] = parts
+            e2e_step()
+        host[:] = parts[lo:hi]
         ce = nb.Counting()
         barrier()
         t1 = time.perf_counter()
         for _ in range(args.steps):
-            w.update_host(host, 0.1, ce)
+            e2e_step(ce)
         barrier()
         e2e_s = allreduce(time.perf_counter() - t1, dist.ReduceOp.MAX if dist else None)
+        e2e_digest = None
+        if sharded:  # the sharded call must leave what the resident steps leave: compared below (parity)
+            import hashlib
+            e2e_digest = hashlib.sha256(host.tobytes()).hexdigest()
+            e2e_final = host.copy()
         w.set_counting(True)
         w.set_particles(parts)
         cr = nb.Counting()
         w.step(args.steps, cr)  # the e2e loop starts from `parts` (no warm-up steps): its own replay
         e2e_inter = allreduce(float(cr.interactions), dist.ReduceOp.SUM if dist else None)
-        e2e = {"value": e2e_inter / e2e_s, "unit": "interactions/s", "h2d_bytes_per_step": 24 * n_total,
-               "d2h_bytes_per_step": 24 * n_total, "ms_per_step": e2e_s / args.steps * 1e3,
-               "steps_per_s": args.steps / e2e_s, "call": "nb_world_update (pinned host nb_particle[])"}
+        per_rank = 24 * (hi - lo)
+        e2e = {"value": e2e_inter / e2e_s, "unit": "interactions/s",
+               "h2d_bytes_per_step": 24 * n_total if sharded or world == 1 else 24 * n_total * world,
+               "d2h_bytes_per_step": 24 * n_total if sharded or world == 1 else 24 * n_total * world,
+               "ms_per_step": e2e_s / args.steps * 1e3,
+               "steps_per_s": args.steps / e2e_s,
+               "call": ("nb_world_update_shard (each rank: its 1/N slice of the Vec in pinned host memory, "
+                        f"{per_rank} B each way per step)" if sharded else "nb_world_update (pinned host nb_particle[])")}
+        if sharded:
+            mine_ok = bool(np.array_equal(w.particles[lo:hi].view(np.uint8), e2e_final.view(np.uint8)))
+            e2e["same_state_as_resident_steps"] = bool(allreduce(1.0 if mine_ok else 0.0, dist.ReduceOp.MIN) == 1.0)
         del host, owner
 
     clocks = sampler.stop() if sampler else None
+
+    # ---- N > 1: is the sharded run the SAME computation?  Every rank steps K times from `parts`, rank 0 repeats
+    # the K steps on one GPU alone, and the SHA-256 digests of the full state (original body order) must agree.
+    parity = None
+    if world > 1 and not args.no_parity:
+        import hashlib
+
+        def digest(wd):
+            x, y, vx, vy, m = wd.get_soa()
+            return hashlib.sha256(x.tobytes() + y.tobytes() + vx.tobytes() + vy.tobytes() + m.tobytes()).digest()
+
+        w.set_counting(False)
+        w.set_particles(parts)
+        barrier()
+        w.step(args.steps)
+        barrier()
+        mine = torch.frombuffer(bytearray(digest(w)), dtype=torch.uint8).cuda()
+        ref = torch.zeros(32, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            w1 = nb.World(n_total, theta=args.theta, dt=0.1, tree=tree, force_mode=force, device=local_rank,
+                          full_sort=args.full_sort)
+            w1.set_counting(False)
+            w1.set_particles(parts)
+            w1.step(args.steps)
+            ref.copy_(torch.frombuffer(bytearray(digest(w1)), dtype=torch.uint8))
+            w1.close()
+        dist.broadcast(ref, 0)
+        same = 1.0 if bool((mine == ref).all().item()) else 0.0
+        same = allreduce(same, dist.ReduceOp.MIN)
+        parity = {"bit_identical_to_1gpu": bool(same == 1.0), "steps": args.steps,
+                  "what": "SHA-256 of x, y, vx, vy, weight of every body (original order) on every rank against a "
+                          "single-GPU run of the same steps by rank 0"}
+
+    # ---- per-kernel device times of one step (events behind every kernel), for the HBM-side rooflines
+    kernel_times = None
+    if world == 1:
+        w.set_counting(False)
+        w.set_particles(parts)
+        w.step(warm)
+        w.flush_l2()
+        kernel_times = w.profile_step()
     # what the builds of the timed steps sorted (one more build of the final state, outside every timed region)
     w.build_tree()
     ti = w.tree_info()
@@ -348,13 +491,14 @@ def main():
         line = {
             "metric": "barnes_hut_body_interactions_per_s", "value": value, "unit": "interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-            "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak" if args.total_bodies is None else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args, n_total), "n_bodies": n_total, "theta": args.theta,
-                       "tree": args.tree, "force_mode": args.force, "parallelism": f"morton-range x{world}" + (f", exchange={args.exchange}" if world > 1 else ""),
-                       "l2": "not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps",
-                       "interaction_count": "from an identical replay of the timed steps with counters on",
-                       "sort": sort_note, "tree_depth": int(ti.max_depth)},
+            "config": workload_config(args, n_total),
+            "details": {"force_mode": args.force, "parallelism": f"morton-range x{world}" + (f", exchange={args.exchange}" if world > 1 else ""),
+                        "l2": "not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps",
+                        "interaction_count": "from an identical replay of the timed steps with counters on",
+                        "sort": sort_note, "tree_depth": int(ti.max_depth), "n_nodes": int(ti.n_nodes)},
             "steps_per_s": args.steps / dev_s,
             "interactions_per_step": inter / args.steps,
             "phases_ms": {"build": c.build_bvh / args.steps * 1e3, "traverse": trav_s * 1e3,
@@ -375,7 +519,13 @@ def main():
         }
         if e2e:
             line["e2e"] = e2e
+        if parity is not None:
+            line["parity"] = parity
+        if kernel_times:
+            line["roofline_hbm"] = hbm_rooflines(kernel_times, n_total, int(ti.n_nodes), float(peaks.get("hbm_gbs", 6650.0)),
+                                                 peak_src)
         if world == 1 and not args.no_cpu_baseline:
+            os.environ.setdefault("NB_ORACLE_NATIVE", "1")  # oracle built for this box's cores
             r = cpu_port_steps(parts, args, 3, 1, 1)
             line["cpu_baseline"] = {
                 "value": r["value"], "unit": "interactions/s", "cores": r["cores"], "kind": "port",
@@ -388,6 +538,8 @@ def main():
     w.close()
     if dist is not None:
         dist.destroy_process_group()
+    if parity is not None and not parity["bit_identical_to_1gpu"]:
+        raise SystemExit(3)
 
 
 if __name__ == "__main__":

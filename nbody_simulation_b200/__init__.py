@@ -191,6 +191,15 @@ class World:
                                          C.byref(counter.c) if counter else None))
         self.n = len(parts)
 
+    def update_host_shard(self, slice_, first, n_total, delta=None, counter=None):
+        """World::update for a Vec sharded over the ranks' hosts (collective): this rank holds bodies
+        [first, first + len(slice_)) of the n_total-body Vec; upload 1/G, NVLink to all, step, download 1/G."""
+        assert slice_.dtype == PARTICLE_DTYPE and slice_.flags["C_CONTIGUOUS"]
+        d = self.cfg.dt if delta is None else float(delta)
+        self._ck(self._L.nb_world_update_shard(self._ctx, slice_.ctypes.data, int(first), len(slice_), int(n_total), d,
+                                               C.byref(counter.c) if counter else None))
+        self.n = int(n_total)
+
     def build_tree(self, counter=None):
         self._ck(self._L.nb_build_tree(self._ctx, C.byref(counter.c) if counter else None))
 

@@ -130,6 +130,45 @@ __global__ void __launch_bounds__(256) integrate_push_kernel(const uint32_t *__r
   out.id[j] = in.id[s];
 }
 
+// nb_world_update_shard: rank r holds bodies [first, first + count) of the caller's Vec.  One kernel splits the AoS
+// records and stores the slice into EVERY rank's state arrays (slot == original index); the u32 weights travel as
+// raw bits through the x array of the other ping-pong buffer (free until the step writes it) and are moved into
+// m[] by unpack_shard_kernel after the hand-shake.
+__global__ void __launch_bounds__(256) push_shard_kernel(const float *__restrict__ aos, PeerOut cur, PeerOut other,
+                                                         int n_ranks, uint32_t first, uint32_t count) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= count) return;
+  const uint32_t i = first + k;
+  const float2 p = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i);
+  const float2 v = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)i + 2);
+  const float w = aos[6 * (size_t)i + 4];
+  for (int r = 0; r < n_ranks; ++r) {
+    cur.x[r][i] = p.x;
+    cur.y[r][i] = p.y;
+    cur.vx[r][i] = v.x;
+    cur.vy[r][i] = v.y;
+    other.x[r][i] = w;
+  }
+}
+__global__ void __launch_bounds__(256) unpack_shard_kernel(BodyArrays b, const float *__restrict__ wbits, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  b.m[i] = __float_as_uint(wbits[i]);
+  b.id[i] = i;
+}
+// Slot order -> ORIGINAL order AoS, only the records whose original index lies in [first, first + count)
+__global__ void __launch_bounds__(256) soa_to_aos_range_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos,
+                                                               uint32_t first, uint32_t count) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const uint32_t id = b.id[s];
+  if (id - first >= count) return;
+  const size_t o = 6 * (size_t)id;
+  *reinterpret_cast<float2 *>(aos + o) = make_float2(b.x[s], b.y[s]);
+  *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(b.vx[s], b.vy[s]);
+  *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
+}
+
 __global__ void peer_signal_kernel(PeerFlags pf, int n_ranks, int rank, uint32_t epoch) {
   if ((int)threadIdx.x < n_ranks) {
     __threadfence_system();

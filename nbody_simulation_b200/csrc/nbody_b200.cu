@@ -890,6 +890,45 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   return NB_OK;
 }
 
+// World::update for a Vec that is sharded over the ranks' hosts: rank r passes bodies [first, first + count) of the
+// n_total-body Vec.  Upload 1/G, NVLink to everybody, step, download 1/G (original order).  Collective.
+int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t count, size_t n_total, float delta,
+                          nb_counting *out) {
+  if (!c || (!slice && count)) return NB_ERR_INVALID;
+  if (n_total > c->cfg.n_max || first + count > n_total) return fail(c, NB_ERR_CAPACITY, "nb_world_update_shard: slice outside n_total <= n_max");
+  if (c->n_ranks < 2 || !c->peer) return fail(c, NB_ERR_INVALID, "nb_world_update_shard: needs the peer mappings (nb_comm_peer_import)");
+  if (c->bvh_ref) return fail(c, NB_ERR_INVALID, "nb_world_update_shard: NB_TREE_BVH_REF keeps the Vec order, use nb_world_update");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->n = (uint32_t)n_total;
+  c->tree_valid = false;
+  if (n_total == 0) return NB_OK;
+  cudaStream_t st = c->stream;
+  auto handshake = [&]() {
+    ++c->peer_epoch;
+    peer_signal_kernel<<<1, 32, 0, st>>>(c->peer_flags_of, c->n_ranks, c->rank, c->peer_epoch);
+    peer_wait_kernel<<<1, 32, 0, st>>>(c->peer_flags, c->n_ranks, c->peer_epoch, c->meta);
+    g_launches += 2;
+  };
+  NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), st));
+  if (count) NB_CUDA(c, cudaMemcpyAsync(c->aos + 6 * first, slice, count * sizeof(nb_particle), cudaMemcpyHostToDevice, st));
+  handshake(); // every rank is inside this call: nobody still reads the arrays the pushes below overwrite
+  if (count)
+    push_shard_kernel<<<cdiv((uint32_t)count, 256), 256, 0, st>>>(c->aos, c->peer_out[c->cur], c->peer_out[c->cur ^ 1],
+                                                                 c->n_ranks, (uint32_t)first, (uint32_t)count);
+  handshake(); // every rank's slice has arrived everywhere
+  unpack_shard_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->body[c->cur ^ 1].x, c->n);
+  g_launches += 2;
+  int rc = do_steps(c, 1, delta, out);
+  if (rc != NB_OK) return rc;
+  if (count) {
+    soa_to_aos_range_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->n, c->aos, (uint32_t)first, (uint32_t)count);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(slice, c->aos + 6 * first, count * sizeof(nb_particle), cudaMemcpyDeviceToHost, st));
+  }
+  NB_CUDA(c, cudaStreamSynchronize(st));
+  return NB_OK;
+}
+
 int nb_build_tree(nb_ctx *c, nb_counting *out) {
   if (!c) return NB_ERR_INVALID;
   NB_CUDA(c, cudaSetDevice(c->device));
