@@ -241,6 +241,18 @@ class World:
         self._ck(self._L.nb_scene_generate_device(self._ctx, int(scene), int(seed), int(n)))
         self.n = int(n)
 
+    def empty(self):
+        """`QuadTree::empty()` (quad_tree.rs:66-89) as a statistic: the count it would return; changes nothing."""
+        v = C.c_uint32()
+        self._ck(self._L.nb_quad_empty(self._ctx, C.byref(v)))
+        return v.value
+
+    def prune(self):
+        """`QuadTree::prune()` (quad_tree.rs:94-137) as a statistic: the count it would return; changes nothing."""
+        v = C.c_uint32()
+        self._ck(self._L.nb_quad_prune(self._ctx, C.byref(v)))
+        return v.value
+
     def profile_step(self):
         """One step with an event behind every kernel: [(name, microseconds), ...] in launch order."""
         buf = (_lib.NbKernelTime * 64)()

@@ -521,6 +521,56 @@ __global__ void draw_compose_kernel(DrawScratch d, const uint32_t *__restrict__ 
   reinterpret_cast<uchar4 *>(frame)[p] = px;
 }
 
+// QuadTree::empty / prune (quad_tree.rs:66-137) as statistics of the freshly built tree: what the two methods
+// would RETURN if the reference ran them on a tree holding exactly this step's bodies after calculate_gravity.
+//   empty(): 1 per node visited; a Root whose total_mass is 0 returns at once (:78-80), so a node is visited iff
+//            every proper ancestor has a non-zero (u32, wrapping) mass.
+//   prune(): 1 per child it drops: Leaf children with count 0 (none exist in a fresh build: children are created
+//            by the first insert into them) and Root children with total_mass 0 (:112-119), found while recursing
+//            only through Roots of non-zero mass below the top node (:120-121).
+__global__ void __launch_bounds__(256) quad_stats_kernel(const Meta *__restrict__ meta, TreeArrays T,
+                                                         unsigned long long *__restrict__ out /* [2] */) {
+  const uint32_t n_nodes = meta->n_nodes;
+  uint32_t e = 0, p = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += gridDim.x * blockDim.x) {
+    const uint4 l = T.link(i);
+    bool anc_all = true, anc_below_top = true; // all proper ancestors / all except the top node have mass != 0
+    for (uint32_t a = l.w; a != 0xffffffffu;) {
+      const uint32_t pa = T.link(a).w;
+      const bool nz = T.mass[a] != 0u;
+      anc_all = anc_all && nz;
+      if (pa != 0xffffffffu) anc_below_top = anc_below_top && nz;
+      a = pa;
+    }
+    e += anc_all ? 1u : 0u;
+    if (i != 0u && !(l.z & kLeafBit) && T.mass[i] == 0u && anc_below_top) p += 1u;
+  }
+  e = __reduce_add_sync(0xffffffffu, e);
+  p = __reduce_add_sync(0xffffffffu, p);
+  if ((threadIdx.x & 31) == 0) {
+    if (e) atomicAdd(&out[0], (unsigned long long)e);
+    if (p) atomicAdd(&out[1], (unsigned long long)p);
+  }
+}
+
+int quad_stats(nb_ctx *c, uint32_t *emptied, uint32_t *pruned) {
+  if (!c->quad) return fail(c, NB_ERR_INVALID, "QuadTree::empty / prune: the context was not created with NB_TREE_QUAD");
+  if (!c->tree_valid) return fail(c, NB_ERR_INVALID, "no valid tree: call nb_build_tree or nb_accel first");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  unsigned long long *d = nullptr, h[2] = {0, 0};
+  NB_CUDA(c, cudaMalloc(&d, 16));
+  NB_CUDA(c, cudaMemsetAsync(d, 0, 16, c->stream));
+  if (c->n) quad_stats_kernel<<<kSMs * 4, 256, 0, c->stream>>>(c->meta, c->T, d);
+  NB_CUDA(c, cudaMemcpyAsync(h, d, 16, cudaMemcpyDeviceToHost, c->stream));
+  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+  cudaFree(d);
+  if (c->n && c->h_meta->n_nodes == 0) h[0] = 1; // all bodies outside the square: the empty top Leaf (:68-72)
+  if (!c->n) h[0] = 1;
+  if (emptied) *emptied = (uint32_t)h[0];
+  if (pruned) *pruned = (uint32_t)h[1];
+  return NB_OK;
+}
+
 } // namespace
 
 // ======================================================================================
@@ -1026,6 +1076,15 @@ int nb_accel_direct(nb_ctx *c, size_t first, size_t count, float *ax, float *ay,
   }
   c->ev_used = 0;
   return NB_OK;
+}
+
+int nb_quad_empty(nb_ctx *c, uint32_t *nodes_visited) {
+  if (!c || !nodes_visited) return NB_ERR_INVALID;
+  return quad_stats(c, nodes_visited, nullptr);
+}
+int nb_quad_prune(nb_ctx *c, uint32_t *children_pruned) {
+  if (!c || !children_pruned) return NB_ERR_INVALID;
+  return quad_stats(c, nullptr, children_pruned);
 }
 
 int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {

@@ -912,6 +912,24 @@ int orc_quad_empty_prune(void *h, uint32_t *emptied, uint32_t *pruned) {
   return 0;
 }
 
+// The same two methods on a FRESH literal tree after calculate_gravity, each on its own: `emptied` = what empty()
+// would return (counted without mutating), then `pruned` = prune() (mutates: do not reuse the handle afterwards).
+static uint32_t quad_empty_visits(const Quad *q) { // quad_tree.rs:66-89, read-only
+  if (q->is_leaf) return 1;
+  if (q->total_mass == 0) return 1;
+  uint32_t sum = 0;
+  for (int i = 0; i < 4; ++i)
+    if (q->children[i]) sum += quad_empty_visits(q->children[i]);
+  return sum + 1;
+}
+int orc_quad_fresh_stats(void *h, uint32_t *emptied, uint32_t *pruned) {
+  OrcTree *T = (OrcTree *)h;
+  if (T->kind != 2) return 1;
+  *emptied = quad_empty_visits(T->qroot);
+  *pruned = quad_prune(T->qroot);
+  return 0;
+}
+
 // ---- direct sums ----------------------------------------------------------------------------
 // fp64 truth of the same force law (main.rs:235-253) on the f32 inputs.
 int orc_direct_f64(const float *x, const float *y, const uint32_t *w, size_t n, const uint32_t *targets,

@@ -58,6 +58,7 @@ def lib():
     L.orc_tree_accel.argtypes = [vp, f, vp, C.c_size_t, C.c_int, vp, vp, P(C.c_uint64), P(C.c_uint64), C.c_int,
                                  P(C.c_double)]
     L.orc_quad_empty_prune.argtypes = [vp, P(C.c_uint32), P(C.c_uint32)]
+    L.orc_quad_fresh_stats.argtypes = [vp, P(C.c_uint32), P(C.c_uint32)]
     L.orc_direct_f64.argtypes = [vp, vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp, C.c_int]
     L.orc_direct_f32.argtypes = [vp, vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp, C.c_int]
     L.orc_world_new.argtypes = [vp, vp, vp, vp, vp, C.c_size_t]
@@ -129,6 +130,12 @@ class Tree:
         self.L.orc_tree_accel(self.h, theta, tp, nt, 1 if literal else 0, ax.ctypes.data, ay.ctypes.data,
                               C.byref(ni), C.byref(ntst), threads, C.byref(sec))
         return ax, ay, ni.value, ntst.value, sec.value
+
+    def fresh_stats(self):
+        """(empty() return value, prune() return value) of the fresh literal quadtree; prune mutates the tree."""
+        e, p = C.c_uint32(), C.c_uint32()
+        assert self.L.orc_quad_fresh_stats(self.h, C.byref(e), C.byref(p)) == 0
+        return e.value, p.value
 
     def empty_prune(self):
         e, p = C.c_uint32(), C.c_uint32()

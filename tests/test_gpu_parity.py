@@ -439,3 +439,19 @@ def test_non_normal_inputs_fast_documented_deviation():
     assert np.isfinite(ax[ok]).all() and np.isfinite(ay[ok]).all()
     assert ob.normwise_err(ax[ok], ay[ok], rx[ok], ry[ok]) <= 1e-5
     w.close()
+
+
+def test_quad_empty_and_prune_report_what_the_reference_would_return():
+    # quad_tree.rs:66-137 on a tree holding this step's bodies; zero-weight regions make Roots of total_mass 0
+    p = scene("disc", 60_000)
+    p["weight"][(p["x"] < 30000) & (p["y"] < 40000)] = 0   # a massless corner: whole subtrees of mass 0
+    p["weight"][:50] = 0
+    for pp in (p, scene("galaxy", 20_000)):
+        w = nb.World(len(pp), theta=0.5, tree=nb.NB_TREE_QUAD)
+        w.set_particles(pp)
+        w.build_tree()
+        T = ob.Tree(ob.KIND_LITERAL_QUAD, pp["x"], pp["y"], pp["weight"])
+        assert T.export()["info"].n_nodes == w.tree_info().n_nodes
+        e, pr = T.fresh_stats()
+        assert (w.empty(), w.prune()) == (e, pr)
+        w.close()
