@@ -36,9 +36,11 @@ struct Meta {
   uint32_t n_leaves;
   uint32_t max_depth;
   uint32_t overflow_leaves;
-  uint32_t error;           // bit 0: node pool too small
+  uint32_t error;           // bit 0: node pool too small; bit 1: this build's top-digit sort was too shallow (the step
+                            // does nothing and the host redoes it with a full sort); bit 2: peer exchange time-out
   uint32_t cog_outside;     // != 0: some internal node's centre of gravity lies outside its box
   uint32_t resort;          // != 0: the top-digit sort of this step was too shallow for the tree (radix_sort.cuh)
+  uint32_t fail_seq;        // sequence number of the first step whose top-digit sort was too shallow (0xffffffff: none)
   uint32_t one;             // 1, written by the host: a loop bound the compiler cannot see through (traverse.cuh)
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)

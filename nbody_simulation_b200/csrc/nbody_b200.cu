@@ -116,6 +116,11 @@ struct nb_ctx {
   int last_top_passes = 0;     // top digits the last build sorted before checking (0 = full sort)
   bool counting = true; // interaction / opening-test counters in the traversal
   unsigned long long seen_interactions = 0, seen_tests = 0;
+  uint32_t step_seq = 0;       // sequence number of the build being enqueued (tree_count_kernel -> Meta::fail_seq)
+  bool resort_hit = false;     // the last synchronisation found a build whose top-digit sort was too shallow
+  uint32_t resort_at = 0;      // ... and this is its sequence number
+  bool redo_next = false, last_redone = false; // the next / the last build is the full-sort redo of a failed guess
+  int redo_guess = 0, last_failed_guess = 0;   // the guess that failed
 
   std::vector<cudaEvent_t> ev; // 5 per timed step, drained in batches
   size_t ev_used = 0;
@@ -242,6 +247,7 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
   NB_CUDA(c, cudaGetLastError());
   c->sorted_in = 0; // the tree order lives in vals[0]
   c->tree_valid = true;
+  ++c->step_seq;
   return NB_OK;
 }
 
@@ -273,6 +279,9 @@ int enqueue_build(nb_ctx *c) {
     if (!sort_can_speculate(make_sort_plan(49), top_passes)) top_passes = 0;
   }
   c->last_top_passes = top_passes;
+  c->last_redone = c->redo_next;
+  c->last_failed_guess = c->redo_guess;
+  c->redo_next = false;
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
                                      c->meta, top_passes);
   c->sorted_in = which;
@@ -281,19 +290,15 @@ int enqueue_build(nb_ctx *c) {
   const uint32_t gb = cdiv(n, 256);
   uint32_t *bbase = c->sort.bsum; // per-256-body block: node count, then (scan_bsum_kernel) the block's first node index
   if (c->quad)
-    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes);
+    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes, c->step_seq);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
   prof_mark(st, "tree_count_kernel");
   scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, c->meta);
   prof_mark(st, "scan_bsum_kernel");
-  if (top_passes) {
-    const uint32_t *cond = &c->meta->resort;
-    radix_sort_fallback(c->keys[0], c->vals[0], c->keys[1], c->vals[1], which, n, 49, top_passes, c->sort, st, cond);
-    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 0, cond);
-    scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, nullptr, cond);
-    g_launches += 2;
-    prof_mark(st, "fallback chain (no-ops unless the depth guess failed)");
-  }
+  // A depth guess that was too shallow (tree_count_kernel raised error bit 1) turns the rest of this step, and of
+  // every step enqueued behind it, into no-ops that leave the state untouched; the host sees it at its next
+  // synchronisation and redoes those steps with a full sort (do_steps, build_tree_checked).  Round 1 enqueued the
+  // full sort + second count behind every build as conditional no-ops: 8 empty launches, ~30 us of a 250 us build.
   // Parent / children / twig links: from the parents' side, either inside the emit kernel (extra searches on the
   // ~30 % of lanes that hold internal nodes) or by tree_link_kernel (chases skip links).  Measured build phase,
   // link kernel vs emit: 1M 0.298 / 0.313 ms, 2M 0.515 / 0.517, 4M 0.813 / 0.807, 8M 1.586 / 1.467 — once the node
@@ -317,6 +322,7 @@ int enqueue_build(nb_ctx *c) {
   prof_mark(st, "tree_finish_kernel");
   NB_CUDA(c, cudaGetLastError());
   c->tree_valid = true;
+  ++c->step_seq;
   return NB_OK;
 }
 
@@ -414,10 +420,20 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
 int sync_and_check(nb_ctx *c) {
   NB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->meta, sizeof(Meta), cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
-  if (c->quad && c->n && c->h_meta->n_nodes) { // the mirror describes the last build enqueued
+  c->resort_hit = false;
+  if (c->h_meta->fail_seq != 0xffffffffu) { // some build since the last check guessed the depth too shallow
+    c->resort_hit = true;
+    c->resort_at = c->h_meta->fail_seq;
+    c->depth_known = false; // the next build sorts every digit
+    c->redo_next = true;
+    c->redo_guess = c->last_top_passes;
+    ++c->resorts;
+    NB_CUDA(c, cudaMemsetAsync(&c->meta->fail_seq, 0xff, sizeof(uint32_t), c->stream));
+    NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), c->stream));
+    c->tree_valid = false;
+  } else if (c->quad && c->n && c->h_meta->n_nodes) { // the mirror describes the last build enqueued
     c->last_max_depth = c->h_meta->max_depth;
     c->depth_known = true;
-    if (c->h_meta->resort) ++c->resorts;
   }
   if (c->h_meta->error & 4u) return fail(c, NB_ERR_NCCL, "peer exchange timed out: a rank did not signal its push within 10 s");
   if (c->h_meta->error & 1u) {
@@ -448,8 +464,8 @@ cudaEvent_t next_event(nb_ctx *c) {
 }
 
 // events are recorded 5 per step: start, after build, after traverse, after integrate, end
-void drain_events(nb_ctx *c, nb_counting *out) {
-  const size_t steps = c->ev_used / 5;
+void drain_events(nb_ctx *c, nb_counting *out, size_t max_steps = (size_t)-1) {
+  const size_t steps = std::min(c->ev_used / 5, max_steps);
   for (size_t s = 0; s < steps; ++s) {
     cudaEvent_t *e = &c->ev[5 * s];
     float ms = 0.f;
@@ -470,28 +486,33 @@ void drain_events(nb_ctx *c, nb_counting *out) {
 int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
   int rc;
   const unsigned long long launches0 = g_launches;
-  for (uint32_t s = 0; s < n_steps; ++s) {
-    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, e3 = nullptr, e4 = nullptr;
-    if (out) {
-      e0 = next_event(c); e1 = next_event(c); e2 = next_event(c); e3 = next_event(c); e4 = next_event(c);
-      if (!e4) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
-      NB_CUDA(c, cudaEventRecord(e0, c->stream));
+  uint32_t remaining = n_steps;
+  while (remaining) {
+    // enqueue a batch blind (no host synchronisation inside a step), then look once
+    const uint32_t batch = std::min(remaining, 256u); // bounds the number of live events
+    const uint32_t seq0 = c->step_seq;
+    for (uint32_t s = 0; s < batch; ++s) {
+      cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, e3 = nullptr, e4 = nullptr;
+      if (out) {
+        e0 = next_event(c); e1 = next_event(c); e2 = next_event(c); e3 = next_event(c); e4 = next_event(c);
+        if (!e4) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+        NB_CUDA(c, cudaEventRecord(e0, c->stream));
+      }
+      if ((rc = enqueue_build(c)) != NB_OK) return rc;
+      if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
+      uint32_t first, count;
+      owned_range(c, first, count);
+      if ((rc = enqueue_traverse(c, first, count)) != NB_OK) return rc;
+      if (out) NB_CUDA(c, cudaEventRecord(e2, c->stream));
+      if ((rc = enqueue_integrate(c, dt, e3)) != NB_OK) return rc;
+      if (out) NB_CUDA(c, cudaEventRecord(e4, c->stream));
     }
-    if ((rc = enqueue_build(c)) != NB_OK) return rc;
-    if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
-    uint32_t first, count;
-    owned_range(c, first, count);
-    if ((rc = enqueue_traverse(c, first, count)) != NB_OK) return rc;
-    if (out) NB_CUDA(c, cudaEventRecord(e2, c->stream));
-    if ((rc = enqueue_integrate(c, dt, e3)) != NB_OK) return rc;
-    if (out) NB_CUDA(c, cudaEventRecord(e4, c->stream));
-    if (out && c->ev_used >= 5 * 256) { // bound the number of live events
-      if ((rc = sync_and_check(c)) != NB_OK) return rc;
-      drain_events(c, out);
-    }
+    if ((rc = sync_and_check(c)) != NB_OK) return rc;
+    // steps from the first too-shallow depth guess on did nothing (state carried over): redo them, full sort first
+    const uint32_t done = c->resort_hit ? std::min(batch, c->resort_at - seq0) : batch;
+    drain_events(c, out, done);
+    remaining -= done;
   }
-  if ((rc = sync_and_check(c)) != NB_OK) return rc;
-  drain_events(c, out);
   absorb_counters(c, out);
   if (out) {
     out->steps += n_steps;
@@ -727,6 +748,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
     }
   }
   Meta m0{};
+  m0.fail_seq = 0xffffffffu;
   m0.x0 = c->cfg.domain_x0; m0.y0 = c->cfg.domain_y0; m0.h = c->cfg.domain_h;
   m0.theta2 = theta_squared(c->cfg.theta);
   m0.one = 1u;
@@ -982,21 +1004,25 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
 int nb_build_tree(nb_ctx *c, nb_counting *out) {
   if (!c) return NB_ERR_INVALID;
   NB_CUDA(c, cudaSetDevice(c->device));
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (out) {
-    e0 = next_event(c); e1 = next_event(c);
-    if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
-    NB_CUDA(c, cudaEventRecord(e0, c->stream));
+  int rc = NB_OK;
+  for (int attempt = 0; attempt < 2; ++attempt) { // a too-shallow depth guess is redone with a full sort
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (out) {
+      e0 = next_event(c); e1 = next_event(c);
+      if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+      NB_CUDA(c, cudaEventRecord(e0, c->stream));
+    }
+    rc = enqueue_build(c);
+    if (rc != NB_OK) return rc;
+    if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
+    rc = sync_and_check(c);
+    if (out && rc == NB_OK) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
+    }
+    c->ev_used = 0;
+    if (rc != NB_OK || !c->resort_hit) break;
   }
-  int rc = enqueue_build(c);
-  if (rc != NB_OK) return rc;
-  if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
-  rc = sync_and_check(c);
-  if (out && rc == NB_OK) {
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
-  }
-  c->ev_used = 0;
   return rc;
 }
 
@@ -1005,26 +1031,33 @@ int nb_accel(nb_ctx *c, float *ax, float *ay, nb_counting *out) {
   NB_CUDA(c, cudaSetDevice(c->device));
   if (c->n == 0) return NB_OK;
   int rc;
-  cudaEvent_t e0 = next_event(c), e1 = next_event(c), e2 = next_event(c);
-  if (!e2) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
-  NB_CUDA(c, cudaEventRecord(e0, c->stream));
-  if (!c->tree_valid && (rc = enqueue_build(c)) != NB_OK) return rc;
-  NB_CUDA(c, cudaEventRecord(e1, c->stream));
-  if ((rc = enqueue_traverse(c, 0, c->n)) != NB_OK) return rc;
-  NB_CUDA(c, cudaEventRecord(e2, c->stream));
-  // scratch: the unsorted ping-pong buffers are free once the tree is built
-  float *dax = reinterpret_cast<float *>(c->keys[c->sorted_in ^ 1]);
-  float *day = dax + c->n_alloc;
-  accel_to_original_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->sacc, c->vals[c->sorted_in],
-                                                                  c->body[c->cur].id, c->n, dax, day);
-  NB_CUDA(c, cudaGetLastError());
-  NB_CUDA(c, cudaMemcpyAsync(ax, dax, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
-  NB_CUDA(c, cudaMemcpyAsync(ay, day, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
-  if ((rc = sync_and_check(c)) != NB_OK) return rc;
-  if (out) {
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
-    if (cudaEventElapsedTime(&ms, e1, e2) == cudaSuccess) out->traverse_s += ms * 1e-3;
+  for (int attempt = 0; attempt < 2; ++attempt) { // a too-shallow depth guess is redone with a full sort
+    cudaEvent_t e0 = next_event(c), e1 = next_event(c), e2 = next_event(c);
+    if (!e2) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
+    NB_CUDA(c, cudaEventRecord(e0, c->stream));
+    if (!c->tree_valid && (rc = enqueue_build(c)) != NB_OK) return rc;
+    NB_CUDA(c, cudaEventRecord(e1, c->stream));
+    if ((rc = enqueue_traverse(c, 0, c->n)) != NB_OK) return rc;
+    NB_CUDA(c, cudaEventRecord(e2, c->stream));
+    // scratch: the unsorted ping-pong buffers are free once the tree is built
+    float *dax = reinterpret_cast<float *>(c->keys[c->sorted_in ^ 1]);
+    float *day = dax + c->n_alloc;
+    accel_to_original_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->sacc, c->vals[c->sorted_in],
+                                                                    c->body[c->cur].id, c->n, dax, day);
+    NB_CUDA(c, cudaGetLastError());
+    NB_CUDA(c, cudaMemcpyAsync(ax, dax, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(c, cudaMemcpyAsync(ay, day, (size_t)c->n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if ((rc = sync_and_check(c)) != NB_OK) return rc;
+    if (c->resort_hit) { // the traversal did nothing: start over (full sort)
+      c->ev_used = 0;
+      continue;
+    }
+    if (out) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) out->build_s += ms * 1e-3;
+      if (cudaEventElapsedTime(&ms, e1, e2) == cudaSuccess) out->traverse_s += ms * 1e-3;
+    }
+    break;
   }
   c->ev_used = 0;
   absorb_counters(c, out);
@@ -1102,8 +1135,8 @@ int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {
   info->max_depth = c->n ? m.max_depth : 0;
   info->overflow_leaves = c->n ? m.overflow_leaves : 0;
   info->root_x0 = m.x0; info->root_y0 = m.y0; info->root_h = m.h;
-  info->sort_top_digits = c->n ? (uint32_t)c->last_top_passes : 0;
-  info->sort_redone = (c->n && c->last_top_passes) ? m.resort : 0;
+  info->sort_top_digits = c->n ? (uint32_t)(c->last_redone ? c->last_failed_guess : c->last_top_passes) : 0;
+  info->sort_redone = (c->n && c->last_redone) ? 1u : 0u;
   return NB_OK;
 }
 

@@ -89,12 +89,12 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
                                                          int cap, uint8_t *__restrict__ leafdepth,
                                                          uint32_t *__restrict__ nstart,
                                                          uint32_t *__restrict__ btotal, int sorted_levels = 0,
-                                                         const uint32_t *cond = nullptr) {
+                                                         uint32_t step_seq = 0) {
   // sorted_levels > 0: the keys are sorted by their top `sorted_levels` levels only (radix_sort.cuh).  Everything
   // below is unaffected as long as every leaf is at most that deep, i.e. no window of cap + 1 consecutive bodies
-  // shares a prefix of sorted_levels or more; a window that does raises meta->resort, and the passes enqueued
-  // behind this one (cond = &meta->resort) redo the sort in full and this count.
-  if (cond && *cond == 0u) return;
+  // shares a prefix of sorted_levels or more; a window that does raises meta->resort and error bit 1: the rest of
+  // the step does nothing (the integrate kernels carry the state over unchanged) and the host, which sees the flag
+  // at its next synchronisation, redoes the steps from `fail_seq` on with a full sort.
   const uint32_t n_in = meta->n_in;
   const uint32_t i0 = blockIdx.x * blockDim.x;
   const uint32_t i = i0 + threadIdx.x;
@@ -109,7 +109,11 @@ __global__ void __launch_bounds__(256) tree_count_kernel(const unsigned long lon
     const long long j = (long long)i0 - cap + t;
     const int8_t wp = (j >= 0 && j + cap < (long long)n_in) ? (int8_t)cpl<BPL>(s_k[t], s_k[t + cap]) : (int8_t)-1;
     s_w[t] = wp;
-    if (sorted_levels > 0 && wp >= sorted_levels) meta->resort = 1u;
+    if (sorted_levels > 0 && wp >= sorted_levels) {
+      meta->resort = 1u;
+      atomicOr(&meta->error, 2u);
+      atomicMin(&meta->fail_seq, step_seq);
+    }
   }
   __syncthreads();
   uint32_t cnt = 0, isleaf = 0, over = 0;
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(256) tree_emit_kernel(const unsigned long long
                                                         const uint32_t *__restrict__ bbase, TreeArrays T) {
   const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
   if (n_nodes > T.capacity) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&meta->error, 1u);
     return;
   }
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -219,8 +223,9 @@ __global__ void __launch_bounds__(256) tree_emit_quad_kernel(const unsigned long
                                                              const uint32_t *__restrict__ nstart,
                                                              const uint32_t *__restrict__ bbase, TreeArrays T) {
   const uint32_t n_in = meta->n_in, n_nodes = meta->n_nodes;
+  if (meta->error & 2u) return; // the sort was too shallow for this tree: the host redoes the step
   if (n_nodes > T.capacity) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) meta->error |= 1u;
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(&meta->error, 1u);
     return;
   }
   __shared__ uint32_t s_excl[kEmitBodies];

@@ -455,3 +455,22 @@ def test_quad_empty_and_prune_report_what_the_reference_would_return():
         e, pr = T.fresh_stats()
         assert (w.empty(), w.prune()) == (e, pr)
         w.close()
+
+
+def test_top_digit_sort_too_shallow_inside_a_batch_of_steps():
+    # nb_step enqueues its steps blind; a depth guess that fails in step k turns steps k.. into no-ops that leave the
+    # state untouched, and the host redoes them (full sort first): same trajectory as a context that always sorts fully
+    shallow, deep = scene("disc", 20_000), scene("plummer", 150_000)
+    ref = nb.World(len(deep), theta=0.5, force_mode=nb.NB_FORCE_EXACT, full_sort=True)
+    ref.set_particles(deep)
+    ref.step(4)
+    w = nb.World(len(deep), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(shallow)
+    w.step(2)             # the depth of the shallow scene is now the guess
+    w.set_particles(deep)
+    c = nb.Counting()
+    w.step(4, c)
+    assert c.steps == 4
+    assert np.array_equal(bits(w.particles), bits(ref.particles))
+    w.close()
+    ref.close()
