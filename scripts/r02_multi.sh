@@ -1,0 +1,12 @@
+# N-GPU pass (round 2): parity at world size N (both exchanges, sharded drop-in call, group walk), then the bench line.
+#   gpurun --gpus N -- 'bash scripts/r02_multi.sh N'
+cd $GRAFT_REPO_ROOT
+N=${1:-2}
+mkdir -p gpurun_out
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+timeout 600 $TR --master-port 29511 tests/multi_gpu_check.py > gpurun_out/multi_gpu_check_$N.log 2>&1; echo "check rc=$?"
+grep -v "^rank [1-9]" gpurun_out/multi_gpu_check_$N.log | tail -22
+timeout 600 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_n$N.err
+python -c "
+import json
+d = json.load(open('gpurun_out/bench_n$N.json')); print(d['n_gpus'], round(d['ms_per_step'], 3), {k: round(v, 3) for k, v in d['phases_ms'].items()}, '%.3e' % d['value'], d.get('parity'), d.get('e2e'))"

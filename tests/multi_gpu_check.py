@@ -58,6 +58,40 @@ def main():
             ok = ok and same and counts_ok
             w.close()
             ref.close()
+    # ---- round 2: the sharded drop-in call (each rank holds 1/G of the Vec on its host) and the group walk ----------
+    for tree, n, mode, grp in [(nb.NB_TREE_QUAD, 100_003, nb.NB_FORCE_EXACT, False), (nb.NB_TREE_LBVH, 50_001, nb.NB_FORCE_FAST, False),
+                               (nb.NB_TREE_QUAD, 100_003, nb.NB_FORCE_FAST, True), (nb.NB_TREE_QUAD, 5, nb.NB_FORCE_EXACT, False)]:
+        p = nb.generate_scene(nb.NB_SCENE_TWO_GALAXY, 4, n)
+        steps = 4
+        w = nb.World(len(p), theta=0.6, dt=0.1, tree=tree, force_mode=mode, device=local, fast_walk_group=grp)
+        uid = torch.zeros(nb._lib.NB_UNIQUE_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.from_numpy(nb.World.comm_unique_id()))
+        dist.broadcast(uid, 0)
+        w.comm_init(rank, world, uid.cpu().numpy())
+        mine = torch.from_numpy(w.comm_peer_export()).cuda()
+        blocks = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(blocks, mine)
+        w.comm_peer_import(torch.stack(blocks).cpu().numpy())
+        lo, hi = rank * len(p) // world, (rank + 1) * len(p) // world
+        host = p[lo:hi].copy()
+        for _ in range(steps):
+            w.update_host_shard(host, lo, len(p), 0.1)
+        ref = nb.World(len(p), theta=0.6, dt=0.1, tree=tree, force_mode=mode, device=local, fast_walk_group=grp)
+        ref.set_particles(p)
+        ref.step(steps)
+        r = ref.particles[lo:hi]
+        same = all(np.array_equal(host[k].view(np.uint32), r[k].view(np.uint32)) for k in ("x", "y", "vx", "vy", "weight"))
+        # and the resident multi-GPU steps with the same walk
+        w.set_particles(p)
+        w.step(steps)
+        q = w.particles[lo:hi]
+        same2 = all(np.array_equal(q[k].view(np.uint32), r[k].view(np.uint32)) for k in ("x", "y", "vx", "vy", "weight"))
+        print(f"rank {rank}/{world} sharded nb_world_update_shard tree={tree} n={len(p)} mode={mode} group_walk={grp} "
+              f"slice=[{lo},{hi}) bit-identical to 1 GPU: host slices {same}, resident steps {same2}", flush=True)
+        ok = ok and same and same2
+        w.close()
+        ref.close()
     flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
