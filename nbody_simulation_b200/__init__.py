@@ -237,9 +237,9 @@ class World:
         return arrays
 
     def generate_on_device(self, scene, seed, n):
-        """Fill the body state on the device (uniform disc / Plummer): no host buffer, no upload."""
+        """Fill the body state on the device (any NB_SCENE_*): no host buffer, no upload."""
         self._ck(self._L.nb_scene_generate_device(self._ctx, int(scene), int(seed), int(n)))
-        self.n = int(n)
+        self.n = int(self._L.nb_body_count(self._ctx))
 
     def empty(self):
         """`QuadTree::empty()` (quad_tree.rs:66-89) as a statistic: the count it would return; changes nothing."""

@@ -152,6 +152,7 @@ def load(path=LIB_PATH):
         "nb_world_update_shard": (C.c_int, [vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, vp]),
         "nb_quad_empty": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
         "nb_quad_prune": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
+        "nb_body_count": (C.c_size_t, [vp]),
         "nb_profile_step": (C.c_int, [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
         "nb_save_snapshot": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
         "nb_load_snapshot": (C.c_int, [vp, C.c_char_p, P(C.c_uint64)]),

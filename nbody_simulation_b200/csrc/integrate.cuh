@@ -2,6 +2,7 @@
 // original-order helpers of the C ABI.
 #pragma once
 #include "common.cuh"
+#include "scan.cuh"
 
 namespace nb {
 
@@ -247,6 +248,102 @@ __global__ void __launch_bounds__(256) scene_kernel(int scene, unsigned long lon
     if (!(y >= 0.f && y < 100000.f)) y = y < 0.f ? 0.f : 99999.99f;
   }
   b.x[i] = x; b.y[i] = y; b.vx[i] = 0.f; b.vy[i] = 0.f; b.m[i] = 1u; b.id[i] = i;
+}
+
+// ---- the two scenes whose host generators draw sequentially (csrc/scene.cpp): default scene (World::new,
+// main.rs:276-346: the grid-disc acceptance is independent per grid point) and the two-galaxy scene (rejection
+// sampling: body i is the i-th ACCEPTED candidate of a counter-based candidate stream).  Both become
+// flag -> scan -> compact over the candidate stream, which reproduces the sequential push order.
+// kind 0: default-scene grid (candidate k = (x - lo) * ny + (y - lo), x outer / y inner as main.rs:317-318)
+// kind 1 / 2: galaxy 0 / 1 of the two-galaxy scene (candidate k = the host loop's `ctr`)
+struct SceneCand { bool ok; float x, y, vx, vy; };
+__device__ __forceinline__ SceneCand scene_candidate(int kind, unsigned long long seed, unsigned long long k,
+                                                     uint32_t lo, uint32_t ny) {
+  SceneCand r{false, 0.f, 0.f, 0.f, 0.f};
+  if (kind == 0) {
+    const uint32_t gx = lo + (uint32_t)(k / ny), gy = lo + (uint32_t)(k % ny);
+    const float px = __fmul_rn((float)gx, 14.0f), py = __fmul_rn((float)gy, 14.0f);
+    const float dx = __fsub_rn(px, 60000.0f), dy = __fsub_rn(py, 60000.0f);
+    const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    if (d2 < 15000000.0f && d2 > 500000.0f) {
+      const float hi_r = __fadd_rn(__fsub_rn(15000000.0f, d2), 1.0f);
+      const float g = __fmul_rn(scene_u01(seed, 0u, (unsigned long long)gx * 8192ull + gy), hi_r);
+      if (g > 6000000.0f) {
+        const float kk = __fsqrt_rn(__fdiv_rn(__fsqrt_rn(750000.0f), d2));
+        r = SceneCand{true, px, py, __fmul_rn(dy, kk), __fmul_rn(-dx, kk)};
+      }
+    }
+  } else {
+    const int g = kind - 1;
+    const float cx = g ? 60000.0f : 35000.0f, cvx = g ? 0.0f : 200.0f, cvy = g ? 0.0f : 250.0f;
+    const float cmf = g ? 750000.0f : 75000000.0f;
+    const double d2s = 500000.0 + (9000000.0 - 500000.0) * (double)scene_u01(seed, 5u + g, 3ull * k);
+    const double keep = 1.0 - 6000000.0 / (15000000.0 - d2s + 1.0);
+    const double t = (double)scene_u01(seed, 5u + g, 3ull * k + 1);
+    if (t < keep) {
+      const double a = 6.283185307179586 * (double)scene_u01(seed, 5u + g, 3ull * k + 2);
+      const double rr = 4.0 * sqrt(d2s);
+      const float px = (float)((double)cx + rr * cos(a)), py = (float)((double)cx + rr * sin(a));
+      const float dx = __fsub_rn(px, cx), dy = __fsub_rn(py, cx);
+      const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+      const float kk = __fsqrt_rn(__fdiv_rn(__fsqrt_rn(cmf), d2));
+      r = SceneCand{true, px, py, __fadd_rn(__fmul_rn(dy, kk), cvx), __fadd_rn(__fmul_rn(-dx, kk), cvy)};
+    }
+  }
+  return r;
+}
+// pass 1 over candidates [k0, k0 + cnt): accept flags -> exclusive prefix inside each 256-block + block totals
+__global__ void __launch_bounds__(256) scene_flag_kernel(int kind, unsigned long long seed, unsigned long long k0,
+                                                         uint32_t cnt, uint32_t lo, uint32_t ny,
+                                                         uint32_t *__restrict__ pre, uint32_t *__restrict__ btotal) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t f = (i < cnt && scene_candidate(kind, seed, k0 + i, lo, ny).ok) ? 1u : 0u;
+  uint32_t tot;
+  const uint32_t ex = block_exclusive_scan<256>(f, tot);
+  if (i < cnt) pre[i] = ex | (f << 31);
+  if (threadIdx.x == 0) btotal[blockIdx.x] = tot;
+}
+// pass 2 (after scan_bsum_kernel turned btotal into block bases): the accepted candidates, in candidate order, become
+// bodies slot0 + emitted + rank while rank stays below `want`; *emitted advances by the chunk's accepted count
+__global__ void __launch_bounds__(256) scene_emit_kernel(int kind, unsigned long long seed, unsigned long long k0,
+                                                         uint32_t cnt, uint32_t lo, uint32_t ny,
+                                                         const uint32_t *__restrict__ pre,
+                                                         const uint32_t *__restrict__ bbase, BodyArrays b, uint32_t slot0,
+                                                         uint32_t want, const uint32_t *__restrict__ emitted) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cnt) return;
+  const uint32_t pv = pre[i];
+  if (!(pv >> 31)) return;
+  const uint32_t rank = *emitted + bbase[blockIdx.x] + (pv & 0x7fffffffu);
+  if (rank >= want) return;
+  const SceneCand c = scene_candidate(kind, seed, k0 + i, lo, ny);
+  const uint32_t s = slot0 + rank;
+  b.x[s] = c.x; b.y[s] = c.y; b.vx[s] = c.vx; b.vy[s] = c.vy; b.m[s] = 1u; b.id[s] = s;
+}
+__global__ void scene_advance_kernel(uint32_t *emitted, const uint32_t *chunk_total) { *emitted += *chunk_total; }
+// the bodies that need no compaction: the heavy cores, and the default scene's 100 000 rand_body draws (main.rs:334-335)
+__global__ void __launch_bounds__(256) scene_fixed_kernel(int scene, unsigned long long seed, BodyArrays b,
+                                                          uint32_t slot0, uint32_t cnt) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) { // main.rs:282-291 (both scenes share the two cores)
+    b.x[0] = 35000.0f; b.y[0] = 35000.0f; b.vx[0] = 200.0f; b.vy[0] = 250.0f; b.m[0] = 75000000u; b.id[0] = 0u;
+    b.x[1] = 60000.0f; b.y[1] = 60000.0f; b.vx[1] = 0.0f; b.vy[1] = 0.0f; b.m[1] = 750000u; b.id[1] = 1u;
+  }
+  if (scene != 0 || i >= cnt) return;
+  // rand_disc (main.rs:255-258) in f32 on the host (cosf / sinf); here fp64 cos / sin rounded to f32
+  const float TAU = 6.28318530717958647692f;
+  float pv[4];
+#pragma unroll
+  for (int st = 0; st < 2; ++st) {
+    const float theta = __fmul_rn(scene_u01(seed, 1u + st, 2ull * i), TAU);
+    const float r = scene_u01(seed, 1u + st, 2ull * i + 1);
+    pv[2 * st] = __fmul_rn((float)cos((double)theta), r);
+    pv[2 * st + 1] = __fmul_rn((float)sin((double)theta), r);
+  }
+  const uint32_t s = slot0 + i;
+  b.x[s] = __fadd_rn(__fmul_rn(pv[0], 25000.0f), 50000.0f);
+  b.y[s] = __fadd_rn(__fmul_rn(pv[1], 25000.0f), 50000.0f);
+  b.vx[s] = pv[2]; b.vy[s] = pv[3]; b.m[s] = 1u; b.id[s] = s;
 }
 
 // Slot order -> AoS in the SAME order: what the reference's Vec looks like after BVHTree::from permuted it.

@@ -864,20 +864,80 @@ int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx
   return NB_OK;
 }
 
-int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) {
-  if (!c) return NB_ERR_INVALID;
-  if (scene != NB_SCENE_UNIFORM_DISC && scene != NB_SCENE_PLUMMER)
-    return fail(c, NB_ERR_INVALID, "nb_scene_generate_device: only the uniform disc and the Plummer scene");
-  if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: n > n_max");
-  NB_CUDA(c, cudaSetDevice(c->device));
-  c->n = (uint32_t)n;
-  c->tree_valid = false;
-  if (n == 0) return NB_OK;
-  scene_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(scene, seed, c->body[c->cur], (uint32_t)n);
-  NB_CUDA(c, cudaGetLastError());
-  NB_CUDA(c, cudaStreamSynchronize(c->stream));
+// compaction of one candidate stream into body slots [slot0, slot0 + want): chunks of at most n_alloc candidates
+// (prefix scratch = vals[0]); returns the number of accepted candidates among the first `limit` (0 = until `want`)
+static int scene_compact(nb_ctx *c, int kind, uint64_t seed, uint32_t lo, uint32_t ny, uint32_t slot0, uint32_t want,
+                         uint64_t limit, uint32_t *accepted) {
+  cudaStream_t st = c->stream;
+  uint32_t *pre = c->vals[0], *bt = c->sort.bsum, *emitted = c->sort.tickets, *chunk_total = c->sort.tickets + 1;
+  NB_CUDA(c, cudaMemsetAsync(emitted, 0, 2 * sizeof(uint32_t), st));
+  const uint32_t chunk = std::min<uint32_t>(c->n_alloc, 1u << 24) / 256u * 256u; // bsum holds n_alloc / 256 + 16 blocks
+  uint64_t k0 = 0;
+  uint32_t got = 0;
+  for (int guard = 0; guard < 100000; ++guard) {
+    const uint32_t cnt = (uint32_t)(limit ? std::min<uint64_t>(chunk, limit - k0) : chunk);
+    if (cnt == 0) break;
+    const uint32_t blocks = cdiv(cnt, 256);
+    scene_flag_kernel<<<blocks, 256, 0, st>>>(kind, seed, k0, cnt, lo, ny, pre, bt);
+    scan_bsum_kernel<<<1, 1024, 0, st>>>(bt, blocks, chunk_total);
+    scene_emit_kernel<<<blocks, 256, 0, st>>>(kind, seed, k0, cnt, lo, ny, pre, bt, c->body[c->cur], slot0, want, emitted);
+    scene_advance_kernel<<<1, 1, 0, st>>>(emitted, chunk_total);
+    NB_CUDA(c, cudaGetLastError());
+    k0 += cnt;
+    if (limit && k0 >= limit) break;
+    if (!limit) { // rejection sampling: stop once enough candidates were accepted (one look per chunk: set-up code)
+      NB_CUDA(c, cudaMemcpyAsync(&got, emitted, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      NB_CUDA(c, cudaStreamSynchronize(st));
+      if (got >= want) break;
+    }
+  }
+  NB_CUDA(c, cudaMemcpyAsync(&got, emitted, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  NB_CUDA(c, cudaStreamSynchronize(st));
+  if (accepted) *accepted = got;
   return NB_OK;
 }
+
+int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) {
+  if (!c) return NB_ERR_INVALID;
+  if (scene != NB_SCENE_DEFAULT && scene != NB_SCENE_UNIFORM_DISC && scene != NB_SCENE_PLUMMER && scene != NB_SCENE_TWO_GALAXY)
+    return fail(c, NB_ERR_INVALID, "nb_scene_generate_device: unknown scene");
+  NB_CUDA(c, cudaSetDevice(c->device));
+  c->tree_valid = false;
+  cudaStream_t st = c->stream;
+  int rc;
+  if (scene == NB_SCENE_DEFAULT) { // World::new (main.rs:276-346): 2 cores + grid disc + 100 000 rand_body; n is ignored
+    const uint32_t lim = (100000u / 14u) - 1u;
+    const uint32_t lo = (uint32_t)((60000.0 - 3900.0) / 14.0), hi = std::min((uint32_t)((60000.0 + 3900.0) / 14.0) + 1u, lim - 1u);
+    const uint32_t ny = hi - lo + 1u;
+    const uint64_t cands = (uint64_t)ny * ny;
+    if (c->cfg.n_max < 100002u) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: the default scene holds ~151k bodies, n_max is too small");
+    const uint32_t room = (uint32_t)std::min<uint64_t>(cands, c->cfg.n_max - 100002u);
+    uint32_t grid = 0;
+    if ((rc = scene_compact(c, 0, seed, lo, ny, 2u, room, cands, &grid)) != NB_OK) return rc;
+    if (grid > room) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: the default scene holds " + std::to_string(grid + 100002u) + " bodies > n_max");
+    scene_fixed_kernel<<<cdiv(100000u, 256), 256, 0, st>>>(0, seed, c->body[c->cur], 2u + grid, 100000u);
+    NB_CUDA(c, cudaGetLastError());
+    c->n = 2u + grid + 100000u;
+  } else if (scene == NB_SCENE_TWO_GALAXY) {
+    if (n < 2) n = 2;
+    if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: n > n_max");
+    const uint32_t per0 = (uint32_t)((n - 2) / 2 + ((n - 2) & 1)), per1 = (uint32_t)((n - 2) / 2);
+    scene_fixed_kernel<<<1, 32, 0, st>>>(1, seed, c->body[c->cur], 0u, 0u);
+    if (per0 && (rc = scene_compact(c, 1, seed, 0u, 1u, 2u, per0, 0, nullptr)) != NB_OK) return rc;
+    if (per1 && (rc = scene_compact(c, 2, seed, 0u, 1u, 2u + per0, per1, 0, nullptr)) != NB_OK) return rc;
+    c->n = (uint32_t)n;
+  } else {
+    if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_scene_generate_device: n > n_max");
+    c->n = (uint32_t)n;
+    if (n == 0) return NB_OK;
+    scene_kernel<<<cdiv((uint32_t)n, 256), 256, 0, st>>>(scene, seed, c->body[c->cur], (uint32_t)n);
+  }
+  NB_CUDA(c, cudaGetLastError());
+  NB_CUDA(c, cudaStreamSynchronize(st));
+  return NB_OK;
+}
+
+size_t nb_body_count(const nb_ctx *c) { return c ? c->n : 0; }
 
 int nb_get_bodies_aos(nb_ctx *c, nb_particle *bodies, size_t n) {
   if (!c || (!bodies && n)) return NB_ERR_INVALID;

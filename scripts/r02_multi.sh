@@ -9,4 +9,4 @@ grep -v "^rank [1-9]" gpurun_out/multi_gpu_check_$N.log | tail -22
 timeout 600 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_n$N.err
 python -c "
 import json
-d = json.load(open('gpurun_out/bench_n$N.json')); print(d['n_gpus'], round(d['ms_per_step'], 3), {k: round(v, 3) for k, v in d['phases_ms'].items()}, '%.3e' % d['value'], d.get('parity'), d.get('e2e'))"
+d = [json.loads(l) for l in open('gpurun_out/bench_n$N.json') if l.startswith('{')][-1]; print(d['n_gpus'], round(d['ms_per_step'], 3), {k: round(v, 3) for k, v in d['phases_ms'].items()}, '%.3e' % d['value'], d.get('parity'), d.get('e2e'))"

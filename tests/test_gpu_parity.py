@@ -316,6 +316,23 @@ def test_device_scene_generation_matches_host(sc, kind):
     w.close()
 
 
+@pytest.mark.parametrize("sc,kind,n", [("galaxy", nb.NB_SCENE_TWO_GALAXY, 300_001), ("galaxy", nb.NB_SCENE_TWO_GALAXY, 2),
+                                       ("default", nb.NB_SCENE_DEFAULT, 0)])
+def test_device_generation_of_the_sequentially_drawn_scenes(sc, kind, n):
+    # two-galaxy (rejection sampling) and World::new's scene (grid acceptance): the same bodies in the same order as
+    # the host's sequential loops; fp64 sin/cos (galaxy) and the default scene's f32 cosf/sinf may differ by one ulp
+    p = scene(sc, n, seed=5)
+    w = nb.World(max(len(p), 200_000))
+    w.generate_on_device(kind, 5, n)
+    q = w.particles
+    assert len(q) == len(p)
+    assert np.array_equal(q["weight"], p["weight"])
+    for k in ("x", "y", "vx", "vy"):
+        d = np.abs(q[k].view(np.int32).astype(np.int64) - p[k].view(np.int32).astype(np.int64))
+        assert d.max() <= 2 and int((d != 0).sum()) <= 2e-3 * len(p) + 5, (k, int(d.max()), int((d != 0).sum()))
+    w.close()
+
+
 # ---- top-digit (speculative) sort of the quadtree build: radix_sort.cuh ---------------------------------------
 @pytest.mark.parametrize("sc,n", [("disc", 200_000), ("plummer", 150_000), ("galaxy", 120_001), ("default", 0)])
 def test_top_digit_sort_builds_the_same_tree(sc, n):
