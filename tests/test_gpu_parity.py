@@ -329,7 +329,10 @@ def test_device_generation_of_the_sequentially_drawn_scenes(sc, kind, n):
     assert np.array_equal(q["weight"], p["weight"])
     for k in ("x", "y", "vx", "vy"):
         d = np.abs(q[k].view(np.int32).astype(np.int64) - p[k].view(np.int32).astype(np.int64))
-        assert d.max() <= 2 and int((d != 0).sum()) <= 2e-3 * len(p) + 5, (k, int(d.max()), int((d != 0).sum()))
+        # glibc's f32 cosf / sinf (default scene, rand_disc) are not correctly rounded: ~1 % of those values sit 1-2 ulp
+        # from the device's fp64-then-round results; the fp64 draws (galaxy) differ for a handful at most
+        lim = 2e-2 * len(p) if sc == "default" else 1e-4 * len(p) + 5
+        assert d.max() <= 2 and int((d != 0).sum()) <= lim, (k, int(d.max()), int((d != 0).sum()))
     w.close()
 
 
