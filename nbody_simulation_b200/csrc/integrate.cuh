@@ -107,28 +107,47 @@ constexpr int kMaxPeers = 8;
 struct PeerOut { float *x[kMaxPeers], *y[kMaxPeers], *vx[kMaxPeers], *vy[kMaxPeers]; };
 struct PeerFlags { uint32_t *flags[kMaxPeers]; }; // flags[r] = rank r's flag array, indexed by the writer's rank
 
+// Round 2: only POSITIONS travel.  A velocity is read once per step, by the rank that integrates the body, so the
+// velocity of slot s stays on the rank that owns position s (owner = s / per, nb_shard_range) and the integrating
+// rank fetches it from there: a local read unless the body crossed a shard boundary in the sort (peer load over
+// NVLink through the same IPC mappings).  Halves the bytes pushed (8 B instead of 16 B per body and peer).
+// Readers of the whole state call pull_velocity_kernel first (ensure_velocities in nbody_b200.cu).
 __global__ void __launch_bounds__(256) integrate_push_kernel(const uint32_t *__restrict__ order,
                                                              const float2 *__restrict__ sacc, BodyArrays in,
-                                                             BodyArrays out, PeerOut po, int n_ranks, uint32_t jfirst,
-                                                             uint32_t jcount, float dt, const Meta *__restrict__ meta) {
+                                                             BodyArrays out, PeerOut pin, PeerOut po, int n_ranks,
+                                                             uint32_t per, uint32_t jfirst, uint32_t jcount, float dt,
+                                                             const Meta *__restrict__ meta) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= jcount) return;
   const uint32_t j = jfirst + k;
   const bool bad = meta->error != 0u; // failed build (the same on every rank): carry the state over unchanged
   const uint32_t s = bad ? j : order[j];
   const float2 a = bad ? make_float2(0.f, 0.f) : sacc[j];
-  const float vx = bad ? in.vx[s] : __fadd_rn(in.vx[s], __fmul_rn(a.x, dt));
-  const float vy = bad ? in.vy[s] : __fadd_rn(in.vy[s], __fmul_rn(a.y, dt));
+  const int o = min((int)(s / per), n_ranks - 1); // the rank that holds slot s's velocity
+  const float vx0 = pin.vx[o][s], vy0 = pin.vy[o][s];
+  const float vx = bad ? vx0 : __fadd_rn(vx0, __fmul_rn(a.x, dt));
+  const float vy = bad ? vy0 : __fadd_rn(vy0, __fmul_rn(a.y, dt));
   const float x = bad ? in.x[s] : __fadd_rn(in.x[s], __fmul_rn(vx, dt));
   const float y = bad ? in.y[s] : __fadd_rn(in.y[s], __fmul_rn(vy, dt));
   for (int r = 0; r < n_ranks; ++r) {
-    po.vx[r][j] = vx;
-    po.vy[r][j] = vy;
     po.x[r][j] = x;
     po.y[r][j] = y;
   }
+  out.vx[j] = vx;
+  out.vy[j] = vy;
   out.m[j] = in.m[s];
   out.id[j] = in.id[s];
+}
+
+// Make the velocities of ALL slots valid on this rank again (after steps whose exchange pushed positions only).
+__global__ void __launch_bounds__(256) pull_velocity_kernel(BodyArrays b, PeerOut pcur, int n_ranks, int rank,
+                                                            uint32_t per, uint32_t n) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const int o = min((int)(s / per), n_ranks - 1);
+  if (o == rank) return;
+  b.vx[s] = pcur.vx[o][s];
+  b.vy[s] = pcur.vy[o][s];
 }
 
 // nb_world_update_shard: rank r holds bodies [first, first + count) of the caller's Vec.  One kernel splits the AoS
@@ -158,15 +177,18 @@ __global__ void __launch_bounds__(256) unpack_shard_kernel(BodyArrays b, const f
   b.id[i] = i;
 }
 // Slot order -> ORIGINAL order AoS, only the records whose original index lies in [first, first + count)
+// (velocities from the rank that holds them, see integrate_push_kernel)
 __global__ void __launch_bounds__(256) soa_to_aos_range_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos,
-                                                               uint32_t first, uint32_t count) {
+                                                               uint32_t first, uint32_t count, PeerOut pcur,
+                                                               int n_ranks, uint32_t per) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   const uint32_t id = b.id[s];
   if (id - first >= count) return;
   const size_t o = 6 * (size_t)id;
+  const int ow = min((int)(s / per), n_ranks - 1);
   *reinterpret_cast<float2 *>(aos + o) = make_float2(b.x[s], b.y[s]);
-  *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(b.vx[s], b.vy[s]);
+  *reinterpret_cast<float2 *>(aos + o + 2) = make_float2(pcur.vx[ow][s], pcur.vy[ow][s]);
   *reinterpret_cast<uint2 *>(aos + o + 4) = make_uint2(b.m[s], 0u);
 }
 

@@ -134,6 +134,7 @@ struct nb_ctx {
   PeerFlags peer_flags_of{};      // every rank's flag array
   uint32_t *peer_flags = nullptr; // this rank's flag array: [r] = epoch of rank r's last completed push
   uint32_t peer_epoch = 0;
+  bool v_partial = false;         // peer exchange: only the velocities of the owned slots are valid here (integrate.cuh)
   std::vector<void *> peer_mapped; // pointers to close in nb_destroy
 
   std::string err;
@@ -177,6 +178,24 @@ int alloc_bodies(nb_ctx *c, BodyArrays &b, size_t n) {
 void free_bodies(BodyArrays &b) {
   cudaFree(b.x); cudaFree(b.y); cudaFree(b.vx); cudaFree(b.vy); cudaFree(b.m); cudaFree(b.id);
   b = BodyArrays{};
+}
+
+// slots per rank of nb_shard_range (also: which rank holds a slot's velocity, integrate.cuh)
+uint32_t shard_per(const nb_ctx *c) {
+  const uint32_t g = (uint32_t)std::max(1, c->n_ranks);
+  return std::max(32u, ((c->n + g - 1) / g + 31u) / 32u * 32u);
+}
+
+// Peer exchange pushes positions only: before anything reads the whole state, fetch the other ranks' velocities.
+int ensure_velocities(nb_ctx *c) {
+  if (!c->v_partial) return NB_OK;
+  c->v_partial = false;
+  if (c->n == 0 || c->n_ranks < 2 || !c->peer) return NB_OK;
+  pull_velocity_kernel<<<(c->n + 255) / 256, 256, 0, c->stream>>>(c->body[c->cur], c->peer_out[c->cur], c->n_ranks, c->rank,
+                                                                 shard_per(c), c->n);
+  g_launches += 1;
+  NB_CUDA(c, cudaGetLastError());
+  return NB_OK;
 }
 
 // owned range of tree positions for this rank
@@ -384,8 +403,10 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   if (c->n_ranks > 1 && c->peer) {
     // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here
     if (count)
-      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, c->peer_out[c->cur ^ 1],
-                                                                    c->n_ranks, first, count, dt, c->meta);
+      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, c->peer_out[c->cur],
+                                                                    c->peer_out[c->cur ^ 1], c->n_ranks, shard_per(c),
+                                                                    first, count, dt, c->meta);
+    c->v_partial = true;
     permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
     ++c->peer_epoch;
@@ -835,6 +856,7 @@ int nb_set_bodies_aos(nb_ctx *c, const nb_particle *bodies, size_t n) {
   if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_set_bodies: n > n_max");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
+  c->v_partial = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
@@ -850,6 +872,7 @@ int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx
   if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_set_bodies: n > n_max");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
+  c->v_partial = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   BodyArrays &b = c->body[c->cur];
@@ -903,6 +926,7 @@ int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) 
     return fail(c, NB_ERR_INVALID, "nb_scene_generate_device: unknown scene");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->tree_valid = false;
+  c->v_partial = false;
   cudaStream_t st = c->stream;
   int rc;
   if (scene == NB_SCENE_DEFAULT) { // World::new (main.rs:276-346): 2 cores + grid disc + 100 000 rand_body; n is ignored
@@ -944,6 +968,7 @@ int nb_get_bodies_aos(nb_ctx *c, nb_particle *bodies, size_t n) {
   if (n < c->n) return fail(c, NB_ERR_CAPACITY, "nb_get_bodies: buffer smaller than body count");
   NB_CUDA(c, cudaSetDevice(c->device));
   if (c->n == 0) return NB_OK;
+  { int rv = ensure_velocities(c); if (rv != NB_OK) return rv; }
   soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
   NB_CUDA(c, cudaGetLastError());
   NB_CUDA(c, cudaMemcpyAsync(bodies, c->aos, (size_t)c->n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
@@ -956,6 +981,7 @@ int nb_get_bodies_soa(nb_ctx *c, float *x, float *y, float *vx, float *vy, uint3
   if (n < c->n) return fail(c, NB_ERR_CAPACITY, "nb_get_bodies: buffer smaller than body count");
   NB_CUDA(c, cudaSetDevice(c->device));
   if (c->n == 0) return NB_OK;
+  { int rv = ensure_velocities(c); if (rv != NB_OK) return rv; }
   BodyArrays &b = c->body[c->cur];
   uint32_t *tmp = c->vals[c->sorted_in ^ 1]; // scratch (the tree order lives in vals[sorted_in])
   const uint32_t *srcs[5] = {(const uint32_t *)b.x, (const uint32_t *)b.y, (const uint32_t *)b.vx,
@@ -1006,6 +1032,7 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   if (n > c->cfg.n_max) return fail(c, NB_ERR_CAPACITY, "nb_world_update: n > n_max");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
+  c->v_partial = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
@@ -1014,6 +1041,7 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   if (rc != NB_OK) return rc;
   // NB_TREE_BVH_REF: the caller's Vec comes back permuted exactly as BVHTree::from leaves it (main.rs:400 hands
   // `self.particles.as_mut()` to the build), because that order is what the next call's tree is built from
+  { int rv = ensure_velocities(c); if (rv != NB_OK) return rv; }
   if (c->bvh_ref) soa_to_aos_slot_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
   else soa_to_aos_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos);
   NB_CUDA(c, cudaGetLastError());
@@ -1032,6 +1060,7 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
   if (c->bvh_ref) return fail(c, NB_ERR_INVALID, "nb_world_update_shard: NB_TREE_BVH_REF keeps the Vec order, use nb_world_update");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n_total;
+  c->v_partial = false;
   c->tree_valid = false;
   if (n_total == 0) return NB_OK;
   cudaStream_t st = c->stream;
@@ -1053,7 +1082,8 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
   int rc = do_steps(c, 1, delta, out);
   if (rc != NB_OK) return rc;
   if (count) {
-    soa_to_aos_range_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->n, c->aos, (uint32_t)first, (uint32_t)count);
+    soa_to_aos_range_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->n, c->aos, (uint32_t)first, (uint32_t)count,
+                                                             c->peer_out[c->cur], c->n_ranks, shard_per(c));
     NB_CUDA(c, cudaGetLastError());
     NB_CUDA(c, cudaMemcpyAsync(slice, c->aos + 6 * first, count * sizeof(nb_particle), cudaMemcpyDeviceToHost, st));
   }
@@ -1275,6 +1305,7 @@ int nb_draw(nb_ctx *c, uint8_t *frame, uint32_t render_h) {
   NB_CUDA(c, dmalloc(&dframe, 4 * (size_t)npix));
   d.hits = buf; d.last = buf + npix; d.heavy = buf + 2 * (size_t)npix;
   NB_CUDA(c, cudaMemsetAsync(buf, 0, 3 * (size_t)npix * 4, c->stream));
+  { int rv = ensure_velocities(c); if (rv != NB_OK) return rv; }
   BodyArrays &b = c->body[c->cur];
   if (n) {
     slot_of_id_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(b.id, n, slot_of);
@@ -1297,6 +1328,7 @@ int nb_save_snapshot(nb_ctx *c, const char *path, uint64_t steps_done) {
     // BVHTree::from starts from the Vec order the previous build left (the partition swaps in place and the f32
     // sums are sequential): the snapshot keeps the SLOT order, with the original index of each body in the pad word
     NB_CUDA(c, cudaSetDevice(c->device));
+    { int rv = ensure_velocities(c); if (rv != NB_OK) return rv; }
     soa_to_aos_slot_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->body[c->cur], c->n, c->aos, true);
     NB_CUDA(c, cudaGetLastError());
     NB_CUDA(c, cudaMemcpyAsync(buf.data(), c->aos, (size_t)c->n * sizeof(nb_particle), cudaMemcpyDeviceToHost, c->stream));
