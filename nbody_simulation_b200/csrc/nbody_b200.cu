@@ -403,9 +403,17 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   if (c->n_ranks > 1 && c->peer) {
     // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here
     if (count)
-      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, c->peer_out[c->cur],
+    {
+      // Where the velocities are read from: the owners' arrays — except right after an upload / pull, when every
+      // rank holds all of them itself and a peer may not even have finished ITS upload yet (no hand-shake between
+      // an upload and the first step): then, and only then, the local arrays.
+      PeerOut pin = c->peer_out[c->cur];
+      if (!c->v_partial)
+        for (int r = 0; r < kMaxPeers; ++r) { pin.vx[r] = in.vx; pin.vy[r] = in.vy; }
+      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, pin,
                                                                     c->peer_out[c->cur ^ 1], c->n_ranks, shard_per(c),
                                                                     first, count, dt, c->meta);
+    }
     c->v_partial = true;
     permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
