@@ -1234,6 +1234,103 @@ int orc_group_walk_leaf_hist(void *h, float theta, int G, double *hist) {
   return 0;
 }
 
+// ---- design tool (round 2): statistics of a group BREADTH-FIRST walk with a conservative group-box classification
+// (sized csrc/traverse_group.cuh; the numbers in profiles/r02a_traverse_group_kernel_ncu.md and DESIGN.md K5 come
+// from here: scripts/group_walk_stats.py).  G tree-order-adjacent bodies share a frontier of (node, mask) entries; an
+// entry is "all accept" when the node passes the opening test for the nearest point of the group's bounding box,
+// "all open" when it fails for the farthest corner, "mixed" otherwise (every body of the mask then decides for
+// itself, exactly as main.rs:370-372).  out[0]=groups, [1]=entries classified, [2]=all-accept with a full mask,
+// [3]=all-accept with a partial mask, [4]=all-open, [5]=mixed, [6]=full-mask items (nodes + leaf bodies),
+// [7]=partial-mask items, [8]=sum of popcounts over partial-mask items, [9]=sum over groups of the largest per-body
+// partial-item count, [10]=frontier batches of 32 entries, [11]=pair interactions, [12]=leaf entries, [13]=sum over
+// groups of the largest per-body item count, [14]=levels.  hist[0][p] / hist[1][p]: node / body items by popcount p.
+int orc_group_bfs_stats(void *h, float theta, int G, double *out, double *hist /* [2][33] */) {
+  OrcTree *T = (OrcTree *)h;
+  const FlatTree &t = T->flat;
+  const size_t n = t.n_in;
+  const int NS = 15;
+  double acc[NS] = {0};
+  const float th2 = theta * theta;
+#pragma omp parallel
+  {
+    double a[NS] = {0};
+    double hl[66] = {0};
+    std::vector<std::pair<uint32_t, uint32_t>> fr, nx;
+    std::vector<uint32_t> pcnt(G), tcnt(G);
+#pragma omp for schedule(dynamic, 64)
+    for (long long g0 = 0; g0 < (long long)n; g0 += G) {
+      int gs = (int)std::min<size_t>(G, n - g0);
+      const uint32_t full = gs == 32 ? 0xffffffffu : ((1u << gs) - 1u);
+      float gx0 = 1e30f, gy0 = 1e30f, gx1 = -1e30f, gy1 = -1e30f;
+      for (int k = 0; k < gs; ++k) {
+        gx0 = std::min(gx0, t.sx[g0 + k]); gx1 = std::max(gx1, t.sx[g0 + k]);
+        gy0 = std::min(gy0, t.sy[g0 + k]); gy1 = std::max(gy1, t.sy[g0 + k]);
+      }
+      for (int k = 0; k < gs; ++k) pcnt[k] = tcnt[k] = 0;
+      a[0] += 1;
+      fr.clear();
+      fr.push_back({0u, full});
+      auto item = [&](uint32_t mask, uint32_t cnt, int isbody) {
+        hl[isbody * 33 + __builtin_popcount(mask)] += cnt;
+        a[11] += (double)__builtin_popcount(mask) * cnt;
+        for (int k = 0; k < gs; ++k) if (mask >> k & 1) tcnt[k] += cnt;
+        if (mask == full) a[6] += cnt;
+        else {
+          a[7] += cnt; a[8] += (double)__builtin_popcount(mask) * cnt;
+          for (int k = 0; k < gs; ++k) if (mask >> k & 1) pcnt[k] += cnt;
+        }
+      };
+      while (!fr.empty()) {
+        a[14] += 1;
+        a[10] += (double)((fr.size() + 31) / 32);
+        nx.clear();
+        for (auto [cur, mask] : fr) {
+          a[1] += 1;
+          if (t.leaf[cur]) { a[12] += 1; item(mask, t.count[cur], 1); continue; }
+          float cx = t.cogx[cur], cy = t.cogy[cur];
+          float ddx = std::max(std::max(gx0 - cx, cx - gx1), 0.f), ddy = std::max(std::max(gy0 - cy, cy - gy1), 0.f);
+          float dmin2 = ddx * ddx + ddy * ddy;
+          float ex = std::max(cx - gx0, gx1 - cx), ey = std::max(cy - gy0, gy1 - cy);
+          float dmax2 = ex * ex + ey * ey;
+          bool disjoint = t.x1[cur] <= gx0 || t.x0[cur] >= gx1 || t.y1[cur] <= gy0 || t.y0[cur] >= gy1;
+          uint32_t open = 0;
+          if (disjoint && t.s2[cur] < dmin2 * th2 * 0.9999f) {
+            a[mask == full ? 2 : 3] += 1;
+            item(mask, 1, 0);
+          } else if (!(t.s2[cur] < dmax2 * th2 * 1.0001f)) {
+            a[4] += 1;
+            open = mask;
+          } else {
+            a[5] += 1;
+            uint32_t am = 0;
+            for (int k = 0; k < gs; ++k) {
+              if (!(mask >> k & 1)) continue;
+              V2 p{t.sx[g0 + k], t.sy[g0 + k]};
+              bool contains = p.y > t.y0[cur] && p.x > t.x0[cur] && p.x < t.x1[cur] && p.y < t.y1[cur];
+              if (!contains && t.s2[cur] < dist2(p, V2{cx, cy}) * theta * theta) am |= 1u << k;
+            }
+            if (am) item(am, 1, 0);
+            open = mask & ~am;
+          }
+          if (open)
+            for (uint32_t c = cur + 1; c < t.skip[cur]; c = t.skip[c]) nx.push_back({c, open});
+        }
+        fr.swap(nx);
+      }
+      uint32_t mp = 0, mt = 0;
+      for (int k = 0; k < gs; ++k) { mp = std::max(mp, pcnt[k]); mt = std::max(mt, tcnt[k]); }
+      a[9] += mp; a[13] += mt;
+    }
+#pragma omp critical
+    {
+      for (int k = 0; k < NS; ++k) acc[k] += a[k];
+      if (hist) for (int k = 0; k < 66; ++k) hist[k] += hl[k];
+    }
+  }
+  for (int k = 0; k < NS; ++k) out[k] = acc[k];
+  return 0;
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
