@@ -1,6 +1,8 @@
 """World-size-2 (and 3) CPU test of the multi-GPU step PROTOCOL over gloo: Morton-range sharding
 (nb_shard_range, the library's own host rule), per-rank traversal + integrate of the owned slice in
-tree order, padded all-gather of (x, y, vx, vy), local permutation of mass/id.  The per-rank compute
+tree order, exchange of the POSITIONS only (padded all-gather of x, y), velocities owned by the rank that owns the
+slot (s // per) and fetched from there by whoever integrates the body, a final pull before the state is read, local
+permutation of mass/id (round 2: integrate_push_kernel / pull_velocity_kernel).  The per-rank compute
 is done by the oracle here (no GPU in this tier); the CUDA implementation of the same protocol is
 checked bit for bit on real GPUs by tests/multi_gpu_check.py."""
 import os
@@ -39,25 +41,33 @@ def _worker(rank, world, port, n, steps, kind, out_dir):
     x, y, vx, vy = (p[k].copy() for k in ("x", "y", "vx", "vy"))
     m, ident = p["weight"].copy(), np.arange(n, dtype=np.uint32)
     per = -(-(-(-n // world)) // 32) * 32  # nb_shard_range: whole 32-body warps
+    def gather(a, count):  # padded all-gather of the owned slices, as ncclAllGather / the peer pushes lay them out
+        send = torch.zeros(per, dtype=torch.float32)
+        send[:count] = torch.from_numpy(a)
+        recv = [torch.zeros(per, dtype=torch.float32) for _ in range(world)]
+        dist.all_gather(recv, send)
+        return torch.cat(recv)[:n].numpy().copy()
+
+    # velocities: after the upload every rank holds all of them; after a step only those of its own slots are valid
+    # here (the others are poisoned on purpose: nothing may read them without fetching from the owner)
+    first, count = nb.shard_range(n, rank, world)
     for _ in range(steps):
         T = ob.Tree(kind, x, y, m)
         order = T.export()["order"]  # tree position -> slot
-        first, count = nb.shard_range(n, rank, world)
         own = order[first:first + count]
+        # "peer loads": the velocity of slot s lives on rank min(s // per, world - 1)
+        vx_all, vy_all = gather(vx[first:first + count], count), gather(vy[first:first + count], count)
         ax, ay, _, _, _ = T.accel(float(theta), own, threads=1)
-        nvx = np.float32(vx[own] + ax * dt)
-        nvy = np.float32(vy[own] + ay * dt)
+        nvx = np.float32(vx_all[own] + ax * dt)
+        nvy = np.float32(vy_all[own] + ay * dt)
         nx = np.float32(x[own] + nvx * dt)
         ny = np.float32(y[own] + nvy * dt)
-        new = []
-        for a in (nx, ny, nvx, nvy):
-            send = torch.zeros(per, dtype=torch.float32)
-            send[:count] = torch.from_numpy(a)
-            recv = [torch.zeros(per, dtype=torch.float32) for _ in range(world)]
-            dist.all_gather(recv, send)
-            new.append(torch.cat(recv)[:n].numpy().copy())
-        x, y, vx, vy = new
+        x, y = gather(nx, count), gather(ny, count)          # positions travel
+        vx = np.full(n, np.nan, np.float32)
+        vy = np.full(n, np.nan, np.float32)
+        vx[first:first + count], vy[first:first + count] = nvx, nvy   # velocities stay
         m, ident = m[order], ident[order]
+    vx, vy = gather(vx[first:first + count], count), gather(vy[first:first + count], count)  # pull_velocity_kernel
     res = np.zeros((5, n), np.float32)
     res[0, ident], res[1, ident], res[2, ident], res[3, ident] = x, y, vx, vy
     res[4, ident] = m.astype(np.float32)
