@@ -27,7 +27,8 @@ w.generate_on_device(nb.NB_SCENE_PLUMMER, 3, 30_000)
 w.step(2)
 w.generate_on_device(nb.NB_SCENE_TWO_GALAXY, 3, 30_000)
 w.step(1)
-print(w.empty(), w.prune() if w.build_tree() is None else 0, len(w.profile_step()))
+w.build_tree()
+print(w.empty(), w.prune(), len(w.profile_step()))
 w.close()
 w = nb.World(200_000)
 w.generate_on_device(nb.NB_SCENE_DEFAULT, 3, 0)
