@@ -285,12 +285,10 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
-  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
-  prof_mark(st, "morton_kernel");
+  g_launches += 5; // morton (+ histogram), count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
   // Quadtree: sort only as many top digits as the previous build's depth (+1 level) needs; tree_count_kernel
-  // verifies, and the conditional passes behind it redo the sort in full if the guess was too shallow
-  // (radix_sort.cuh).  Digit p from the top covers 4 quadtree levels (the top digit also holds the outside bit).
+  // verifies, and the host redoes the step with a full sort if the guess was too shallow (radix_sort.cuh).  Digit p
+  // from the top covers 4 quadtree levels (the top digit also holds the outside bit).
   int top_passes = 0;
   if (c->quad && c->depth_known && !c->cfg.full_sort) {
     const int want = ((int)c->last_max_depth + 1 + 3) / 4;
@@ -301,8 +299,14 @@ int enqueue_build(nb_ctx *c) {
   c->last_redone = c->redo_next;
   c->last_failed_guess = c->redo_guess;
   c->redo_next = false;
-  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
-                                     c->meta, top_passes);
+  const int key_bits = c->quad ? 49 : 48;
+  const SortPlan plan = make_sort_plan(key_bits);
+  const int first_pass = sort_prepare(n, key_bits, c->sort, st, top_passes);
+  morton_hist_kernel<<<cdiv(cdiv(n, 4), 256), 256, plan.hist_total * sizeof(uint32_t), st>>>(
+      b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0], plan, first_pass, c->sort.ghist);
+  prof_mark(st, "morton_hist_kernel");
+  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, key_bits, c->sort, st,
+                                     c->meta, top_passes, true);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
@@ -312,7 +316,13 @@ int enqueue_build(nb_ctx *c) {
     tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes, c->step_seq);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
   prof_mark(st, "tree_count_kernel");
-  scan_bsum_kernel<<<1, 1024, 0, st>>>(bbase, gb, &c->meta->n_nodes, c->meta);
+  { // block bases + meta->n_nodes: chunks of 1024 block totals, then their bases (scan.cuh)
+    const uint32_t chunks = cdiv(gb, 1024u);
+    uint32_t *ctot = bbase + gb; // bsum holds n_alloc / 256 + n_alloc / 262144 + 64 words: chunk totals behind the block totals
+    scan_chunks_kernel<<<chunks, 1024, 0, st>>>(bbase, gb, ctot);
+    scan_bases_kernel<<<chunks, 1024, 0, st>>>(bbase, gb, ctot, &c->meta->n_nodes);
+    g_launches += 1;
+  }
   prof_mark(st, "scan_bsum_kernel");
   // A depth guess that was too shallow (tree_count_kernel raised error bit 1) turns the rest of this step, and of
   // every step enqueued behind it, into no-ops that leave the state untouched; the host sees it at its next
@@ -734,7 +744,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->sort.ghist, (size_t)4096));
   NB_TRY(dmalloc(&c->sort.tickets, (size_t)16));
   NB_TRY(dmalloc(&c->sort.status, c->sort.status_words));
-  NB_TRY(dmalloc(&c->sort.bsum, na / 256 + 16)); // block totals of tree_count_kernel (256 bodies) / of the flag scan
+  NB_TRY(dmalloc(&c->sort.bsum, na / 256 + na / 262144 + 64)); // block totals of tree_count_kernel (256 bodies) / of the flag scan
   const size_t ncap = 2 * na + 65536;
   c->T.capacity = (uint32_t)std::min<size_t>(ncap, 0xfffffff0u);
   NB_TRY(dmalloc(&c->T.box, (size_t)c->T.capacity));

@@ -71,4 +71,33 @@ __global__ void __launch_bounds__(1024) scan_bsum_kernel(uint32_t *__restrict__ 
   }
 }
 
+// Two-launch version for the tree build (round 2): one block of 1024 is 33 us at 8M bodies (31 250 block totals walked
+// by a single CTA).  scan_chunks_kernel scans each 1024-entry chunk in place and leaves the chunk totals;
+// scan_bases_kernel adds to every chunk the sum of the totals before it (a few dozen values, summed by each block
+// itself) and the last block writes the grand total (+ the statistics reset of a resorted build is gone: round 2).
+__global__ void __launch_bounds__(1024) scan_chunks_kernel(uint32_t *__restrict__ bsum, uint32_t nb,
+                                                           uint32_t *__restrict__ ctot) {
+  const uint32_t i = blockIdx.x * 1024u + threadIdx.x;
+  const uint32_t v = (i < nb) ? bsum[i] : 0u;
+  uint32_t tot;
+  const uint32_t ex = block_exclusive_scan<1024>(v, tot);
+  if (i < nb) bsum[i] = ex;
+  if (threadIdx.x == 0) ctot[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(1024) scan_bases_kernel(uint32_t *__restrict__ bsum, uint32_t nb,
+                                                          const uint32_t *__restrict__ ctot, uint32_t *total_out) {
+  __shared__ uint32_t base_s;
+  if (threadIdx.x < 32) { // chunks before this one (at most n / 262 144 of them: a handful)
+    uint32_t a = 0;
+    for (uint32_t j = threadIdx.x; j < blockIdx.x; j += 32) a += ctot[j];
+    a = __reduce_add_sync(0xffffffffu, a);
+    if (threadIdx.x == 0) base_s = a;
+  }
+  __syncthreads();
+  const uint32_t base = base_s;
+  const uint32_t i = blockIdx.x * 1024u + threadIdx.x;
+  if (i < nb) bsum[i] += base;
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0 && total_out) *total_out = base + ctot[blockIdx.x];
+}
+
 } // namespace nb
