@@ -165,7 +165,8 @@ def hbm_rooflines(kernel_times, n, n_nodes, hbm_gbs, peak_src):
     """Achieved HBM GB/s of the step's memory-bound kernels: ALGORITHMIC bytes (SURVEY.md §8 d) over the
     device time nb_profile_step measured for each (one step, events behind every kernel, L2 flushed before)."""
     per_body = {  # bytes per body
-        "morton_hist_kernel": 20.0,     # x, y read (8) + key (8) + slot index (4) written; digit histograms in smem
+        "morton_kernel": 20.0,          # x, y read (8) + key (8) + slot index (4) written
+        "sort_histogram_kernel": 8.0,   # one read of the keys, the digits of the passes that run
         "sort_onesweep_kernel": 24.0,   # (key, slot) read + written
         "tree_count_kernel": 13.0,      # key read (8) + leaf depth (1) + node-count prefix (4) written
         "integrate_resort_kernel": 60.0,  # order 4 + acc 8 + 24 gathered + 24 written

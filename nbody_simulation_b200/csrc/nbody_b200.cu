@@ -285,7 +285,7 @@ int enqueue_build(nb_ctx *c) {
     bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
-  g_launches += 5; // morton (+ histogram), count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
+  g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
   // Quadtree: sort only as many top digits as the previous build's depth (+1 level) needs; tree_count_kernel
   // verifies, and the host redoes the step with a full sort if the guess was too shallow (radix_sort.cuh).  Digit p
   // from the top covers 4 quadtree levels (the top digit also holds the outside bit).
@@ -299,14 +299,10 @@ int enqueue_build(nb_ctx *c) {
   c->last_redone = c->redo_next;
   c->last_failed_guess = c->redo_guess;
   c->redo_next = false;
-  const int key_bits = c->quad ? 49 : 48;
-  const SortPlan plan = make_sort_plan(key_bits);
-  const int first_pass = sort_prepare(n, key_bits, c->sort, st, top_passes);
-  morton_hist_kernel<<<cdiv(cdiv(n, 4), 256), 256, plan.hist_total * sizeof(uint32_t), st>>>(
-      b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0], plan, first_pass, c->sort.ghist);
-  prof_mark(st, "morton_hist_kernel");
-  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, key_bits, c->sort, st,
-                                     c->meta, top_passes, true);
+  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
+  prof_mark(st, "morton_kernel");
+  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
+                                     c->meta, top_passes);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];

@@ -19,7 +19,6 @@
 #pragma once
 #include "common.cuh"
 #include "scan.cuh"
-#include "morton.cuh"
 
 namespace nb {
 
@@ -61,79 +60,15 @@ inline SortPlan make_sort_plan(int key_bits) { // 8-bit digits; a 9-bit last dig
 
 // All passes' histograms in one read of the keys.
 __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long *__restrict__ keys, uint32_t n,
-                                                             SortPlan plan, uint32_t *__restrict__ ghist) {
+                                                             SortPlan plan, uint32_t *__restrict__ ghist,
+                                                             int first_pass = 0 /* only the passes that will run */) {
   extern __shared__ uint32_t sh[];
   for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const unsigned long long k = keys[i];
-    for (int p = 0; p < plan.passes; ++p)
+    for (int p = first_pass; p < plan.passes; ++p)
       atomicAdd(&sh[plan.hist_off[p] + ((uint32_t)(k >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x)
-    if (sh[i]) atomicAdd(&ghist[i], sh[i]);
-}
-
-// K1 + the histogram in one kernel (round 2): the keys are histogrammed where they are made instead of being read
-// back by sort_histogram_kernel (-8 B per body, one launch less).  Bodies arrive nearly sorted (slot order = tree order
-// of the previous step), so the lanes of a warp mostly share their upper digits: a plain shared-memory atomicAdd per
-// key serialises 32-way on those bins (sort_histogram_kernel ran at 0.07 of the copy bandwidth for that reason);
-// here the lanes with equal digits elect one of them (__match_any_sync) to add their count.  Only the digits of the
-// passes that will run (first_pass .. passes - 1) are counted.
-__global__ void __launch_bounds__(256) morton_hist_kernel(const float *__restrict__ x, const float *__restrict__ y,
-                                                          const Meta *__restrict__ meta, uint32_t n, int quad_mode,
-                                                          unsigned long long *__restrict__ keys,
-                                                          uint32_t *__restrict__ vals, SortPlan plan, int first_pass,
-                                                          uint32_t *__restrict__ ghist) {
-  extern __shared__ uint32_t sh[];
-  for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x) sh[i] = 0;
-  __syncthreads();
-  const float x0 = meta->x0, y0 = meta->y0, h = meta->h;
-  const uint32_t i4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
-  const unsigned lane = threadIdx.x & 31;
-  unsigned long long kk[4] = {0ull, 0ull, 0ull, 0ull};
-  if (i4 < n) {
-    float px[4], py[4];
-    if (i4 + 3 < n) {
-      const float4 vx = *reinterpret_cast<const float4 *>(x + i4);
-      const float4 vy = *reinterpret_cast<const float4 *>(y + i4);
-      px[0] = vx.x; px[1] = vx.y; px[2] = vx.z; px[3] = vx.w;
-      py[0] = vy.x; py[1] = vy.y; py[2] = vy.z; py[3] = vy.w;
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        px[k] = (i4 + k < n) ? x[i4 + k] : 0.f;
-        py[k] = (i4 + k < n) ? y[i4 + k] : 0.f;
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      kk[k] = morton_chain(px[k], py[k], x0, y0, h);
-      if (quad_mode && !in_domain(px[k], py[k], x0, y0, h)) kk[k] = kKeyOut;
-    }
-    if (i4 + 3 < n) {
-      reinterpret_cast<ulonglong2 *>(keys + i4)[0] = make_ulonglong2(kk[0], kk[1]);
-      reinterpret_cast<ulonglong2 *>(keys + i4)[1] = make_ulonglong2(kk[2], kk[3]);
-      *reinterpret_cast<uint4 *>(vals + i4) = make_uint4(i4, i4 + 1, i4 + 2, i4 + 3);
-    } else {
-      for (int k = 0; k < 4 && i4 + k < n; ++k) {
-        keys[i4 + k] = kk[k];
-        vals[i4 + k] = i4 + k;
-      }
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const bool valid = i4 + k < n;
-    const unsigned vm = __ballot_sync(0xffffffffu, valid);
-    if (valid) {
-      for (int p = first_pass; p < plan.passes; ++p) {
-        const uint32_t d = (uint32_t)(kk[k] >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
-        const unsigned same = __match_any_sync(vm, d);
-        if (lane == (unsigned)(__ffs(same) - 1)) atomicAdd(&sh[plan.hist_off[p] + d], (uint32_t)__popc(same));
-      }
-    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < plan.hist_total; i += blockDim.x)
@@ -350,8 +285,7 @@ inline bool sort_can_speculate(const SortPlan &plan, int top_passes) {
 // Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
 inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
                             uint32_t *vals_b, uint32_t n, int bits, const SortScratch &sc, cudaStream_t st,
-                            Meta *meta = nullptr, int top_passes = 0, bool hist_done = false) {
-  // hist_done: sort_prepare() + morton_hist_kernel already zeroed the scratch and filled the histograms
+                            Meta *meta = nullptr, int top_passes = 0) {
   if (n == 0) return 0;
   const SortPlan plan = make_sort_plan(bits);
   const int rounds = sort_rounds_for(n);
@@ -361,16 +295,11 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
   const int first = spec ? plan.passes - top_passes : 0;
   size_t need = 0;
   for (int p = first; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
-  if (spec) // the fallback passes' look-back state
-    for (int p = 0; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
-  if (!hist_done) {
-    cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);
-    cudaMemsetAsync(sc.status, 0, need * sizeof(uint32_t), st);
-    const uint32_t hblocks = tiles < (uint32_t)kSMs * 4u ? tiles : (uint32_t)kSMs * 4u;
-    g_launches += 1;
-    sort_histogram_kernel<<<hblocks, 256, plan.hist_total * sizeof(uint32_t), st>>>(keys_a, n, plan, sc.ghist);
-  }
-  g_launches += 1 + (plan.passes - first);
+  cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);
+  cudaMemsetAsync(sc.status, 0, need * sizeof(uint32_t), st);
+  const uint32_t hblocks = tiles < (uint32_t)kSMs * 4u ? tiles : (uint32_t)kSMs * 4u;
+  g_launches += 2 + (plan.passes - first);
+  sort_histogram_kernel<<<hblocks, 256, plan.hist_total * sizeof(uint32_t), st>>>(keys_a, n, plan, sc.ghist, first);
   sort_scan_hist_kernel<<<plan.passes, 512, 0, st>>>(sc.ghist, plan, sc.tickets, meta, n);
   prof_mark(st, "sort_histogram_kernel");
   unsigned long long *kin = keys_a, *kout = keys_b;
@@ -387,21 +316,6 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
     prof_mark(st, "sort_onesweep_kernel");
   }
   return which;
-}
-
-// Zero the histogram and look-back scratch of a sort of n keys with `top_passes` (0 = all) and return the first pass
-// that will run: what morton_hist_kernel needs before radix_sort_pairs(..., hist_done = true).
-inline int sort_prepare(uint32_t n, int bits, const SortScratch &sc, cudaStream_t st, int top_passes) {
-  const SortPlan plan = make_sort_plan(bits);
-  const int rounds = sort_rounds_for(n);
-  const uint32_t tile_elems = (uint32_t)(kSortThreads * rounds);
-  const uint32_t tiles = (n + tile_elems - 1) / tile_elems;
-  const int first = sort_can_speculate(plan, top_passes) ? plan.passes - top_passes : 0;
-  size_t need = 0;
-  for (int p = first; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
-  cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);
-  cudaMemsetAsync(sc.status, 0, need * sizeof(uint32_t), st);
-  return first;
 }
 
 // After radix_sort_pairs(..., top_passes) returned `which`: the full sort, every pass conditional on *cond
