@@ -226,6 +226,23 @@ __global__ void __launch_bounds__(256) aos_to_soa_kernel(const float *__restrict
   b.x[i] = p.x; b.y[i] = p.y; b.vx[i] = v.x; b.vy[i] = v.y; b.m[i] = w.x; b.id[i] = id_from_pad ? w.y : i;
 }
 
+// After an upload the state sits in CALLER order, and everything behind the sort would gather it through `order`
+// four bytes at a time — a 32-byte sector per word: at 64M bodies tree_finish_kernel and integrate_resort_kernel
+// moved 14x their algorithmic bytes that way (profiles/r01e_64m_kernels.md).  While the uploaded AoS copy is still
+// in HBM, ONE pass gathers whole 24-byte records in tree order into the other SoA buffer and makes `order` the
+// identity, so every later kernel of the step reads coalesced.
+__global__ void __launch_bounds__(256) permute_from_aos_kernel(const float *__restrict__ aos, uint32_t *__restrict__ order,
+                                                               BodyArrays out, uint32_t n) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const uint32_t s = order[j];
+  const float2 p = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)s);
+  const float2 v = *reinterpret_cast<const float2 *>(aos + 6 * (size_t)s + 2);
+  const uint32_t w = __float_as_uint(aos[6 * (size_t)s + 4]);
+  out.x[j] = p.x; out.y[j] = p.y; out.vx[j] = v.x; out.vy[j] = v.y; out.m[j] = w; out.id[j] = s;
+  order[j] = j;
+}
+
 // Slot order -> ORIGINAL body order AoS.
 __global__ void __launch_bounds__(256) soa_to_aos_kernel(BodyArrays b, uint32_t n, float *__restrict__ aos) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;

@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -134,6 +135,8 @@ struct nb_ctx {
   PeerFlags peer_flags_of{};      // every rank's flag array
   uint32_t *peer_flags = nullptr; // this rank's flag array: [r] = epoch of rank r's last completed push
   uint32_t peer_epoch = 0;
+  bool aos_fresh = false;         // c->aos holds the uploaded records of the CURRENT state (caller order == slot order)
+  uint32_t aos_permute_min = 1u << 21; // bodies from which the first build after an upload re-orders through the AoS copy
   bool v_partial = false;         // peer exchange: only the velocities of the owned slots are valid here (integrate.cuh)
   std::vector<void *> peer_mapped; // pointers to close in nb_destroy
 
@@ -270,19 +273,24 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
   return NB_OK;
 }
 
+inline uint32_t gb_of(uint32_t n) { return (n + 255u) / 256u; }
+
 int enqueue_build(nb_ctx *c) {
   const uint32_t n = c->n;
   cudaStream_t st = c->stream;
-  BodyArrays &b = c->body[c->cur];
   if (n == 0) return NB_OK;
   // a failed build is not sticky: every build starts with a clean error word (the failed step itself left the
   // state untouched, see copy_body in integrate.cuh)
   NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), st));
-  if (c->bvh_ref) return enqueue_build_bvh_ref(c);
+  if (c->bvh_ref) {
+    c->aos_fresh = false;
+    return enqueue_build_bvh_ref(c);
+  }
+  BodyArrays &b0 = c->body[c->cur]; // the state as it is stored now (caller order right after an upload)
   if (!c->quad && c->cfg.domain_auto) {
     const int np = kSMs * 4;
     g_launches += 2;
-    bounds_partial_kernel<<<np, 256, 0, st>>>(b.x, b.y, n, c->bounds_partial);
+    bounds_partial_kernel<<<np, 256, 0, st>>>(b0.x, b0.y, n, c->bounds_partial);
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
   g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
@@ -299,13 +307,22 @@ int enqueue_build(nb_ctx *c) {
   c->last_redone = c->redo_next;
   c->last_failed_guess = c->redo_guess;
   c->redo_next = false;
-  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
+  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b0.x, b0.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
   prof_mark(st, "morton_kernel");
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
                                      c->meta, top_passes);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
+  const bool reorder = c->aos_fresh && n >= c->aos_permute_min;
+  c->aos_fresh = false;
+  if (reorder) { // first build after an upload: bring the state into tree order once, through the AoS copy
+    permute_from_aos_kernel<<<gb_of(n), 256, 0, st>>>(c->aos, order, c->body[c->cur ^ 1], n);
+    c->cur ^= 1;
+    g_launches += 1;
+    prof_mark(st, "permute_from_aos_kernel");
+  }
+  BodyArrays &b = c->body[c->cur];
   const uint32_t gb = cdiv(n, 256);
   uint32_t *bbase = c->sort.bsum; // per-256-body block: node count, then (scan_bsum_kernel) the block's first node index
   if (c->quad)
@@ -714,6 +731,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   nb_ctx *c = new nb_ctx();
   c->cfg = *cfg;
   c->device = cfg->device;
+  if (const char *e = std::getenv("NB_B200_AOS_PERMUTE_MIN")) c->aos_permute_min = (uint32_t)std::strtoul(e, nullptr, 10);
   c->quad = cfg->tree_kind == NB_TREE_QUAD;
   c->bvh_ref = cfg->tree_kind == NB_TREE_BVH_REF;
   c->leaf_cap = cfg->leaf_cap ? cfg->leaf_cap : (c->quad ? 8 : 64); // MAX_CAPACITY / TARGET_POINTS
@@ -871,10 +889,12 @@ int nb_set_bodies_aos(nb_ctx *c, const nb_particle *bodies, size_t n) {
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
   c->v_partial = false;
+  c->aos_fresh = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
   aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
+  c->aos_fresh = true;
   NB_CUDA(c, cudaGetLastError());
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
   return NB_OK;
@@ -887,6 +907,7 @@ int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
   c->v_partial = false;
+  c->aos_fresh = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   BodyArrays &b = c->body[c->cur];
@@ -1047,10 +1068,12 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n;
   c->v_partial = false;
+  c->aos_fresh = false;
   c->tree_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
   aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
+  c->aos_fresh = true;
   int rc = do_steps(c, 1, delta, out);
   if (rc != NB_OK) return rc;
   // NB_TREE_BVH_REF: the caller's Vec comes back permuted exactly as BVHTree::from leaves it (main.rs:400 hands
@@ -1075,6 +1098,7 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
   NB_CUDA(c, cudaSetDevice(c->device));
   c->n = (uint32_t)n_total;
   c->v_partial = false;
+  c->aos_fresh = false;
   c->tree_valid = false;
   if (n_total == 0) return NB_OK;
   cudaStream_t st = c->stream;
