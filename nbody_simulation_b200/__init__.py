@@ -110,7 +110,7 @@ class World:
         cfg.force_mode, cfg.device = int(force_mode), int(device)
         cfg.faithful_index_bug = 1 if faithful_index_bug else 0
         cfg.full_sort = 1 if full_sort else 0
-        cfg.fast_walk_group = 1 if fast_walk_group else 0
+        cfg.fast_walk_group = int(fast_walk_group)
         self.cfg = cfg
         self._ctx = self._L.nb_create(C.byref(cfg))
         if not self._ctx:

@@ -383,6 +383,14 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
                                                            first, count)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
+  if (!ex && !c->bvh_ref && c->cfg.fast_walk_group == 2) {
+    // hybrid: far field by lane-parallel classification + dense lists, near field by the depth-first walk
+    const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);
+    if (c->counting)
+      traverse_hybrid_kernel<true><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
+    else
+      traverse_hybrid_kernel<false><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
+  } else
   if (!ex && !c->bvh_ref && c->cfg.fast_walk_group) {
     // list-then-evaluate group walk (traverse_group.cuh): quadtree and LBVH in NB_FORCE_FAST
     const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);

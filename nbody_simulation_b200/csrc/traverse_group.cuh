@@ -257,6 +257,268 @@ __device__ __forceinline__ void traverse_group_body(const float4 *__restrict__ b
   }
 }
 
+// ---- hybrid (round 2, second attempt): far field as above, near field by the depth-first walk ---------------------
+// The group walk pays for itself in the far field (items every body takes: dense broadcast evaluation, one
+// classification per node) and loses in the near field, where the decisions are ragged per body.  So: phase 1 is the
+// lane-parallel classification restricted to nodes reached through nodes that EVERY body opens — masks stay full,
+// accepted nodes and the bodies of fully opened leaves / twigs go to the F list — and every node on which the bodies
+// disagree becomes a ROOT; phase 2 walks each root's subtree with the per-lane depth-first walk of
+// traverse_fast_kernel (own decision per lane, `resume` mask).  Per-body decisions, and therefore interaction and
+// test counts, are those of the reference walk; sums are in list order, then root by root.
+constexpr int kHybStack = 384; // node indices (u32)
+constexpr int kHybF = 160;     // F items
+constexpr int kHybRoots = 64;  // roots of disagreement awaiting their depth-first walk
+struct HybSmem { // per warp: 1.5 + 2.5 + 0.25 KB
+  uint32_t stack[kHybStack];
+  float4 F[kHybF];
+  uint32_t roots[kHybRoots];
+};
+
+// the walk of traverse_fast_body over the subtree [cur, end): same instruction sequence, end instead of n_nodes
+template <bool COUNT, bool CONTAINS>
+__device__ __forceinline__ void hyb_dfs(const float4 *__restrict__ box, const float4 *__restrict__ node,
+                                        const float4 *__restrict__ sbody, const float theta2, const float px,
+                                        const float py, const float2 np, const bool valid, uint32_t cur,
+                                        const uint32_t end, const uint32_t one, float &ax, float &ay, uint32_t &n_inter,
+                                        uint32_t &n_test) {
+  uint32_t resume = valid ? 0u : 0xffffffffu;
+  while (cur < end) {
+    float4 c;
+    uint4 l;
+    load_node(node + 2 * (size_t)cur, c, l);
+    const bool active = cur >= resume;
+    const float2 dn = __fadd2_rn(make_float2(c.x, c.y), np);
+    const float dx = dn.x, dy = dn.y;
+    const float d2 = fmaf(dy, dy, dx * dx);
+    bool far = c.w < d2 * theta2;
+    if (CONTAINS) {
+      const float4 bx = box[cur];
+      far = far && !(py > bx.y && px > bx.x && px < bx.z && py < bx.w);
+    }
+    if (l.z & (kLeafBit | kTwigBit)) {
+      const bool twig = !(l.z & kLeafBit);
+      const bool acc = twig && active && far;
+      if (acc) force_from_diff<false>(dx, dy, d2, c.z, ax, ay);
+      const bool take = active && !(twig && far);
+      const uint32_t k = l.z & kCountMask;
+      if (COUNT) {
+        n_test += (twig && active) ? 1u : 0u;
+        n_inter += (acc ? 1u : 0u) + (take ? k : 0u);
+      }
+      if (__any_sync(0xffffffffu, take)) {
+        uint32_t jb = l.y;
+        float lx = ax, ly = ay;
+#pragma unroll 1
+        for (uint32_t o = k & one; o != 0u; --o) {
+          const float4 b0 = sbody[jb++];
+          const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), np);
+          const float dx0 = e0.x, dy0 = e0.y;
+          const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
+          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
+        }
+        const float4 *bp = sbody + jb;
+#pragma unroll 1
+        for (uint32_t j = k >> 1; j != 0u; --j, bp += 2) {
+          const float4 b0 = bp[0];
+          const float4 b1 = bp[1];
+          const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), np), e1 = __fadd2_rn(make_float2(b1.x, b1.y), np);
+          const float dx0 = e0.x, dy0 = e0.y, dx1 = e1.x, dy1 = e1.y;
+          const float w0 = b0.z * rcp_approx(fmaf(fabsf(dx0) + fabsf(dy0), fmaxf(fmaf(dy0, dy0, dx0 * dx0), 0.001f), 1e-20f));
+          const float w1 = b1.z * rcp_approx(fmaf(fabsf(dx1) + fabsf(dy1), fmaxf(fmaf(dy1, dy1, dx1 * dx1), 0.001f), 1e-20f));
+          lx = fmaf(dx0, w0, lx); ly = fmaf(dy0, w0, ly);
+          lx = fmaf(dx1, w1, lx); ly = fmaf(dy1, w1, ly);
+        }
+        ax = take ? lx : ax;
+        ay = take ? ly : ay;
+      }
+      cur = l.x;
+    } else {
+      const bool acc = active && far;
+      if (acc) {
+        force_from_diff<false>(dx, dy, d2, c.z, ax, ay);
+        resume = l.x;
+      }
+      if (COUNT) {
+        n_test += active ? 1u : 0u;
+        n_inter += acc ? 1u : 0u;
+      }
+      cur = __any_sync(0xffffffffu, active && !far) ? cur + 1 : l.x;
+    }
+  }
+}
+
+template <bool COUNT, bool CONTAINS>
+__device__ __forceinline__ void traverse_hybrid_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
+                                                     const uint4 *__restrict__ kids, Meta *meta,
+                                                     const float4 *__restrict__ sbody, float2 *__restrict__ sacc,
+                                                     const float theta2, const uint32_t tfirst, const uint32_t tcount,
+                                                     HybSmem &S) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
+  if (t0 >= tcount) return;
+  const bool valid = (t0 + lane) < tcount;
+  const uint32_t t = tfirst + (valid ? (t0 + lane) : t0);
+  const float4 me = sbody[t];
+  const float px = me.x, py = me.y;
+  const float2 np = make_float2(-px, -py);
+  const uint32_t nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+  float gx0 = px, gx1 = px, gy0 = py, gy1 = py;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    gx0 = fminf(gx0, __shfl_xor_sync(0xffffffffu, gx0, o));
+    gx1 = fmaxf(gx1, __shfl_xor_sync(0xffffffffu, gx1, o));
+    gy0 = fminf(gy0, __shfl_xor_sync(0xffffffffu, gy0, o));
+    gy1 = fmaxf(gy1, __shfl_xor_sync(0xffffffffu, gy1, o));
+  }
+  const float th_acc = theta2 * 0.99999f, th_open = theta2 * 1.00001f;
+  const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t one = 1u | ((meta->one >> 31) << 8);
+  float ax = 0.f, ay = 0.f;
+  uint32_t n_inter = 0, n_test = 0;   // per lane (phase 2)
+  uint32_t u_inter = 0, u_test = 0;   // per group (phase 1): every valid body takes part
+  uint32_t top = 0, fcnt = 0, rcnt = 0;
+  if (meta->n_nodes != 0u) {
+    if (lane == 0) S.stack[0] = 0u;
+    top = 1;
+  }
+  __syncwarp();
+  while (top != 0u) {
+    const int room = (kHybStack - 72 - (int)top) / 3; // as in traverse_group_body
+    const uint32_t p = min(min(32u, top), (uint32_t)max(room, 1));
+    const bool have = lane < p;
+    uint32_t ni = 0u;
+    if (have) ni = S.stack[top - 1u - lane];
+    top -= p;
+    __syncwarp();
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 l = make_uint4(0u, 0u, 0u, 0u);
+    if (have) load_node(node + 2 * (size_t)ni, c, l);
+    bool acc = false, open = false, root = false;
+    uint32_t rk = 0u;
+    if (have) {
+      if (l.z & kLeafBit) {
+        rk = l.z & kCountMask;
+      } else {
+        const float ux = gx0 - c.x, vx = c.x - gx1, uy = gy0 - c.y, vy = c.y - gy1;
+        const float nx = fmaxf(fmaxf(ux, vx), 0.f), ny = fmaxf(fmaxf(uy, vy), 0.f);
+        const float fx = fmaxf(-ux, -vx), fy = fmaxf(-uy, -vy);
+        const float dmin2 = fmaf(ny, ny, nx * nx), dmax2 = fmaf(fy, fy, fx * fx);
+        acc = c.w < dmin2 * th_acc;
+        if (CONTAINS) {
+          const float4 bx = box[ni];
+          acc = acc && (bx.z <= gx0 || bx.x >= gx1 || bx.w <= gy0 || bx.y >= gy1);
+        }
+        open = !acc && !(c.w < dmax2 * th_open);
+        root = !acc && !open;
+        if (open && (l.z & kTwigBit)) { // every body sums every body below the twig
+          rk = l.z & kCountMask;
+          open = false;
+        }
+      }
+    }
+    if (COUNT) {
+      u_test += __popc(__ballot_sync(0xffffffffu, have && !(l.z & kLeafBit) && !root)); // roots are tested in phase 2
+      u_inter += __popc(__ballot_sync(0xffffffffu, acc));
+    }
+    { // accepted by every body -> F
+      const uint32_t bf = __ballot_sync(0xffffffffu, acc);
+      if (fcnt + 32u > (uint32_t)kHybF) {
+        __syncwarp();
+        eval_full(S.F, fcnt, np, ax, ay);
+        fcnt = 0;
+        __syncwarp();
+      }
+      if (acc) S.F[fcnt + __popc(bf & lt)] = make_float4(c.x, c.y, c.z, 0.f);
+      fcnt += __popc(bf);
+    }
+    { // the bodies disagree -> a root for phase 2
+      const uint32_t br = __ballot_sync(0xffffffffu, root);
+      if (br) {
+        if (rcnt + 32u > (uint32_t)kHybRoots) {
+          __syncwarp();
+          for (uint32_t r = 0; r < rcnt; ++r) {
+            const uint32_t rn = S.roots[r];
+            const uint32_t end = __ldg(reinterpret_cast<const uint32_t *>(node + 2 * (size_t)rn + 1));
+            hyb_dfs<COUNT, CONTAINS>(box, node, sbody, theta2, px, py, np, valid, rn, end, one, ax, ay, n_inter, n_test);
+          }
+          rcnt = 0;
+          __syncwarp();
+        }
+        if (root) S.roots[rcnt + __popc(br & lt)] = ni;
+        rcnt += __popc(br);
+      }
+    }
+    { // opened by every body -> children
+      uint4 kd = make_uint4(kNoKid, kNoKid, kNoKid, kNoKid);
+      if (open) kd = kids[ni];
+      const uint32_t kq[4] = {kd.x, kd.y, kd.z, kd.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const bool v = kq[q] != kNoKid;
+        const uint32_t b = __ballot_sync(0xffffffffu, v);
+        if (v) S.stack[top + __popc(b & lt)] = kq[q];
+        top += __popc(b);
+      }
+    }
+    uint32_t rb = __ballot_sync(0xffffffffu, rk != 0u);
+    while (rb) { // body ranges every body takes -> F (coalesced copies)
+      const int j = __ffs(rb) - 1;
+      rb &= rb - 1u;
+      const uint32_t first = __shfl_sync(0xffffffffu, l.y, j), k = __shfl_sync(0xffffffffu, rk, j);
+      if (COUNT) u_inter += k;
+      for (uint32_t off = 0; off < k; off += 32u) {
+        const uint32_t nn = min(32u, k - off);
+        if (fcnt + 32u > (uint32_t)kHybF) {
+          __syncwarp();
+          eval_full(S.F, fcnt, np, ax, ay);
+          fcnt = 0;
+          __syncwarp();
+        }
+        if (lane < nn) S.F[fcnt + lane] = sbody[first + off + lane];
+        fcnt += nn;
+      }
+    }
+    __syncwarp();
+  }
+  eval_full(S.F, fcnt, np, ax, ay);
+  for (uint32_t r = 0; r < rcnt; ++r) {
+    const uint32_t rn = S.roots[r];
+    const uint32_t end = __ldg(reinterpret_cast<const uint32_t *>(node + 2 * (size_t)rn + 1)); // link.x = skip
+    hyb_dfs<COUNT, CONTAINS>(box, node, sbody, theta2, px, py, np, valid, rn, end, one, ax, ay, n_inter, n_test);
+  }
+  if (valid) sacc[t] = make_float2(ax, ay);
+  if (COUNT) {
+    unsigned long long wi = n_inter, wt = n_test;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      wi += __shfl_xor_sync(0xffffffffu, wi, o);
+      wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&meta->interactions, wi + (unsigned long long)u_inter * nvalid);
+      atomicAdd(&meta->node_tests, wt + (unsigned long long)u_test * nvalid);
+    }
+  }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kGrpWarps * 32) traverse_hybrid_kernel(const float4 *__restrict__ box,
+                                                                         const float4 *__restrict__ node,
+                                                                         const uint4 *__restrict__ kids, Meta *meta,
+                                                                         const float4 *__restrict__ sbody,
+                                                                         float2 *__restrict__ sacc, uint32_t tfirst,
+                                                                         uint32_t tcount) {
+  if (meta->error) return;
+  __shared__ HybSmem smem[kGrpWarps];
+  HybSmem &S = smem[threadIdx.x >> 5];
+  const float theta2 = meta->theta2;
+  node = static_cast<const float4 *>(meta->node_base); // as traverse_fast_kernel: a loaded base stays in its register
+  if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0)
+    traverse_hybrid_body<COUNT, true>(box, node, kids, meta, sbody, sacc, theta2, tfirst, tcount, S);
+  else
+    traverse_hybrid_body<COUNT, false>(box, node, kids, meta, sbody, sacc, theta2, tfirst, tcount, S);
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(kGrpWarps * 32) traverse_group_kernel(const float4 *__restrict__ box,
                                                                         const float4 *__restrict__ node,

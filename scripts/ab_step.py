@@ -24,7 +24,7 @@ ap.add_argument("--tree", default="quad", choices=["quad", "lbvh", "bvhref"])
 ap.add_argument("--theta", type=float, default=0.5)
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--reps", type=int, default=3)
-ap.add_argument("--group", action="store_true", help="NB_FORCE_FAST with the list-then-evaluate group walk instead of the depth-first walk")
+ap.add_argument("--group", type=int, default=0, help="NB_FORCE_FAST walk: 0 depth-first, 1 group walk, 2 hybrid (group far field + depth-first near field)")
 args = ap.parse_args()
 scene = {"disc": nb.NB_SCENE_UNIFORM_DISC, "plummer": nb.NB_SCENE_PLUMMER}[args.scene]
 tree = {"quad": nb.NB_TREE_QUAD, "lbvh": nb.NB_TREE_LBVH, "bvhref": nb.NB_TREE_BVH_REF}[args.tree]
@@ -49,7 +49,7 @@ for _ in range(args.reps):
         best = r
 x, y, vx, vy, _ = w.get_soa()
 state = hashlib.sha256(x.tobytes() + y.tobytes() + vx.tobytes() + vy.tobytes()).hexdigest()[:16]
-print(json.dumps({"lib": os.environ.get("NB_B200_LIB", "in-tree"), "workload": f"{args.n} {args.scene} {args.tree} theta={args.theta}" + (" group" if args.group else ""),
+print(json.dumps({"lib": os.environ.get("NB_B200_LIB", "in-tree"), "workload": f"{args.n} {args.scene} {args.tree} theta={args.theta}" + (f" walk{args.group}" if args.group else ""),
                   "interactions": int(cc.interactions), "accel_sha": digest, "state_sha": state,
                   **{k: round(v, 4) for k, v in best.items()}}))
 w.close()

@@ -398,16 +398,17 @@ def test_group_walk_makes_the_same_decisions(tree, okind, theta):
     # interactions of its private walk (counts equal the depth-first FAST kernel's), sums within 1e-5 of the oracle
     p = scene("galaxy", 150_001)  # ragged last warp
     res = []
-    for grp in (False, True):
+    for grp in (0, 1, 2):  # depth-first, group walk, hybrid (group far field + depth-first near field)
         w = nb.World(len(p), theta=theta, tree=tree, force_mode=nb.NB_FORCE_FAST, fast_walk_group=grp)
         w.set_particles(p)
         c = nb.Counting()
         ax, ay = w.accel(c)
         res.append((ax, ay, int(c.interactions), int(c.node_tests)))
         w.close()
-    assert res[0][2] == res[1][2] and res[0][3] == res[1][3]
+    assert res[0][2] == res[1][2] == res[2][2] and res[0][3] == res[1][3] == res[2][3]
     rx, ry, _, _, _ = ob.Tree(okind, p["x"], p["y"], p["weight"]).accel(theta)
     assert ob.normwise_err(res[1][0], res[1][1], rx, ry) <= 1e-5
+    assert ob.normwise_err(res[2][0], res[2][1], rx, ry) <= 1e-5
 
 
 def nonnormal_scene():
