@@ -17,6 +17,7 @@ NB_FORCE_EXACT, NB_FORCE_FAST = 0, 1
 NB_SCENE_DEFAULT, NB_SCENE_UNIFORM_DISC, NB_SCENE_PLUMMER, NB_SCENE_TWO_GALAXY = range(4)
 NB_UNIQUE_ID_BYTES = 128
 NB_PEER_BLOCK_BYTES = 640
+NB_NOALLOC_MAX_TARGETS = 65536
 
 # struct nb_particle (24 B) == reference `Particle` (src/main.rs:193-198)
 PARTICLE_DTYPE = np.dtype(
@@ -153,6 +154,7 @@ def load(path=LIB_PATH):
         "nb_quad_empty": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
         "nb_quad_prune": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
         "nb_body_count": (C.c_size_t, [vp]),
+        "nb_accel_direct_noalloc": (C.c_int, [vp, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int32, vp, vp, vp]),
         "nb_profile_step": (C.c_int, [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
         "nb_save_snapshot": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
         "nb_load_snapshot": (C.c_int, [vp, C.c_char_p, P(C.c_uint64)]),

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1538,3 +1539,111 @@ int nb_comm_owned_range(nb_ctx *c, uint64_t *first, uint64_t *count) {
 }
 
 } // extern "C"
+
+// ======================================================================================
+// Allocation-free direct sum (no counterpart in the reference).
+// nb_accel_direct cudaMallocs its fp64 accumulators on every call; callers that must not allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc) get the same tiled O(N^2) sum with the accumulators in a
+// file-scope device array instead.  The array is held by every GPU that loads the library until the process exits.
+// ======================================================================================
+namespace {
+
+constexpr uint32_t kNoAllocMaxTargets = NB_NOALLOC_MAX_TARGETS; // 2 doubles each: 1 MiB
+static __device__ __align__(256) double g_noalloc_acc[2 * (size_t)kNoAllocMaxTargets];
+
+// In host code `g_noalloc_acc` is a host-side stand-in, NOT a device address: the kernels get the address
+// cudaGetSymbolAddress returns, looked up once per device with that device current.
+constexpr int kNoAllocMaxDevices = 64;
+double *g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+
+// direct_kernel (direct.cuh) with the targets named by position instead of through a slot table: target t is body
+// first + t of the arrays passed in.  Same tiles, same fp32 pair terms and per-tile partial sums, same fp64
+// accumulation across tiles and source chunks.
+template <bool EXACT>
+__global__ void __launch_bounds__(kDirectThreads) direct_noalloc_kernel(const float *__restrict__ x,
+                                                                        const float *__restrict__ y,
+                                                                        const uint32_t *__restrict__ m, uint32_t n,
+                                                                        uint32_t first, uint32_t nt,
+                                                                        double *__restrict__ acc, uint32_t chunk) {
+  __shared__ float4 tile[kDirectThreads];
+  const uint32_t t = blockIdx.x * kDirectThreads + threadIdx.x;
+  const bool valid = t < nt;
+  const uint32_t slot = first + (valid ? t : 0u);
+  const float px = x[slot], py = y[slot];
+  const uint32_t s0 = blockIdx.y * chunk;
+  const uint32_t s1 = (s0 + chunk < n) ? s0 + chunk : n;
+  double dax = 0.0, day = 0.0;
+  for (uint32_t base = s0; base < s1; base += kDirectThreads) {
+    const uint32_t j = base + threadIdx.x;
+    tile[threadIdx.x] = (j < s1) ? make_float4(x[j], y[j], (float)m[j], 0.f) : make_float4(px, py, 0.f, 0.f);
+    __syncthreads();
+    const uint32_t cnt = (s1 - base < (uint32_t)kDirectThreads) ? s1 - base : (uint32_t)kDirectThreads;
+    float fax = 0.f, fay = 0.f;
+    if (cnt == (uint32_t)kDirectThreads) {
+#pragma unroll 8
+      for (int q = 0; q < kDirectThreads; ++q) {
+        const float4 b = tile[q];
+        pair_force<EXACT>(px, py, b.x, b.y, b.z, fax, fay);
+      }
+    } else {
+      for (uint32_t q = 0; q < cnt; ++q) {
+        const float4 b = tile[q];
+        pair_force<EXACT>(px, py, b.x, b.y, b.z, fax, fay);
+      }
+    }
+    dax += (double)fax;
+    day += (double)fay;
+    __syncthreads();
+  }
+  if (valid) {
+    atomicAdd(&acc[2 * (size_t)t], dax);
+    atomicAdd(&acc[2 * (size_t)t + 1], day);
+  }
+}
+
+} // namespace
+
+extern "C" int nb_accel_direct_noalloc(const float *d_x, const float *d_y, const uint32_t *d_weight, size_t n,
+                                       size_t first, size_t count, int32_t force_mode, float *d_ax, float *d_ay,
+                                       void *stream) {
+  if (count == 0) return NB_OK;
+  if (!d_x || !d_y || !d_weight || !d_ax || !d_ay) return fail(nullptr, NB_ERR_INVALID, "nb_accel_direct_noalloc: null pointer");
+  if (force_mode != NB_FORCE_EXACT && force_mode != NB_FORCE_FAST) return fail(nullptr, NB_ERR_INVALID, "nb_accel_direct_noalloc: force_mode");
+  if (count > kNoAllocMaxTargets)
+    return fail(nullptr, NB_ERR_CAPACITY,
+                "nb_accel_direct_noalloc: " + std::to_string(count) + " targets exceed NB_NOALLOC_MAX_TARGETS = " +
+                    std::to_string(kNoAllocMaxTargets) + " (the static scratch array); split the call or use nb_accel_direct");
+  if (n > 0xffffffffull || first + count > n) return fail(nullptr, NB_ERR_CAPACITY, "nb_accel_direct_noalloc: targets outside [0, n) or n >= 2^32");
+  int dev = 0;
+  NB_CUDA(nullptr, cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(nullptr, NB_ERR_INVALID, "nb_accel_direct_noalloc: device ordinal out of range");
+  double *acc = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev]) { // set-up, once per device, with that device current
+      double *p = nullptr;
+      NB_CUDA(nullptr, cudaGetSymbolAddress((void **)&p, g_noalloc_acc));
+      g_noalloc_ptr[dev] = p;
+    }
+    acc = g_noalloc_ptr[dev];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const uint32_t un = (uint32_t)n, nt = (uint32_t)count;
+  // the array keeps the last call's sums: the accumulators of this call's targets start at zero
+  NB_CUDA(nullptr, cudaMemsetAsync(acc, 0, 2 * (size_t)nt * sizeof(double), st));
+  const uint32_t tblocks = cdiv(nt, kDirectThreads);
+  uint32_t ychunks = std::max(1u, std::min(cdiv(un, 4096u), cdiv((uint32_t)kSMs * 8u, tblocks)));
+  ychunks = std::min(ychunks, 65535u);
+  const uint32_t chunk = cdiv(cdiv(un, ychunks), kDirectThreads) * kDirectThreads;
+  ychunks = cdiv(un, chunk);
+  const dim3 grid(tblocks, ychunks);
+  if (force_mode == NB_FORCE_EXACT)
+    direct_noalloc_kernel<true><<<grid, kDirectThreads, 0, st>>>(d_x, d_y, d_weight, un, (uint32_t)first, nt, acc, chunk);
+  else
+    direct_noalloc_kernel<false><<<grid, kDirectThreads, 0, st>>>(d_x, d_y, d_weight, un, (uint32_t)first, nt, acc, chunk);
+  direct_finish_kernel<<<cdiv(nt, 256), 256, 0, st>>>(acc, nt, d_ax, d_ay);
+  g_launches += 2;
+  NB_CUDA(nullptr, cudaGetLastError());
+  return NB_OK;
+}
