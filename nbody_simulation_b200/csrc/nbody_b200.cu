@@ -1117,24 +1117,45 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
     peer_wait_kernel<<<1, 32, 0, st>>>(c->peer_flags, c->n_ranks, c->peer_epoch, c->meta);
     g_launches += 2;
   };
+  // NB_B200_SHARD_TIMING=1: device time of the call's phases on stderr (debug aid; events only when asked for)
+  static const bool timing = std::getenv("NB_B200_SHARD_TIMING") != nullptr;
+  cudaEvent_t tev[6] = {};
+  auto mark = [&](int k) {
+    if (!timing) return;
+    cudaEventCreate(&tev[k]);
+    cudaEventRecord(tev[k], st);
+  };
+  mark(0);
   NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), st));
   if (count) NB_CUDA(c, cudaMemcpyAsync(c->aos + 6 * first, slice, count * sizeof(nb_particle), cudaMemcpyHostToDevice, st));
+  mark(1);
   handshake(); // every rank is inside this call: nobody still reads the arrays the pushes below overwrite
+  mark(2);
   if (count)
     push_shard_kernel<<<cdiv((uint32_t)count, 256), 256, 0, st>>>(c->aos, c->peer_out[c->cur], c->peer_out[c->cur ^ 1],
                                                                  c->n_ranks, (uint32_t)first, (uint32_t)count);
   handshake(); // every rank's slice has arrived everywhere
   unpack_shard_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->body[c->cur ^ 1].x, c->n);
   g_launches += 2;
+  mark(3);
   int rc = do_steps(c, 1, delta, out);
   if (rc != NB_OK) return rc;
+  mark(4);
   if (count) {
     soa_to_aos_range_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->n, c->aos, (uint32_t)first, (uint32_t)count,
                                                              c->peer_out[c->cur], c->n_ranks, shard_per(c));
     NB_CUDA(c, cudaGetLastError());
     NB_CUDA(c, cudaMemcpyAsync(slice, c->aos + 6 * first, count * sizeof(nb_particle), cudaMemcpyDeviceToHost, st));
   }
+  mark(5);
   NB_CUDA(c, cudaStreamSynchronize(st));
+  if (timing) {
+    float ms[5] = {};
+    for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&ms[k], tev[k], tev[k + 1]);
+    std::fprintf(stderr, "[shard timing] rank %d: h2d %.3f  wait-all-in %.3f  push+wait %.3f  step %.3f  gather+d2h %.3f ms\n",
+                 c->rank, ms[0], ms[1], ms[2], ms[3], ms[4]);
+    for (cudaEvent_t e : tev) cudaEventDestroy(e);
+  }
   return NB_OK;
 }
 
