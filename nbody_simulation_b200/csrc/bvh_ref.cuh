@@ -705,6 +705,16 @@ __global__ void __launch_bounds__(kSubThreads) bvh_subtree_kernel(BvhWork W, uin
   }
 }
 
+// ---- the host enqueued `levels` levels without looking (as many as the previous build needed, plus one): were they
+// enough?  If big nodes remain, the rest of this step does nothing (error bit 1, as for a too-shallow sort guess in
+// tree_build.cuh) and the host redoes it with the synchronising loop.
+__global__ void bvh_levels_check_kernel(const BvhWork W, Meta *meta, int levels, uint32_t step_seq) {
+  if (threadIdx.x == 0 && blockIdx.x == 0 && levels <= kBvhMaxLevels && W.meta->cnt_big[levels] != 0u) {
+    atomicOr(&meta->error, 2u);
+    atomicMin(&meta->fail_seq, step_seq);
+  }
+}
+
 // ---- subtree sizes, atomic bottom-up -----------------------------------------------------------------
 __global__ void __launch_bounds__(256) bvh_sizes_kernel(BvhWork W) {
   const uint32_t nn = min(W.meta->n_nodes, W.node_cap);
@@ -727,6 +737,7 @@ __global__ void __launch_bounds__(256) bvh_sizes_kernel(BvhWork W) {
 // ---- pre-order index by climbing to the root, then emit into the traversal's arrays ------------------
 // order[] (position -> storage slot) is what the finish kernel gathers through.
 __global__ void __launch_bounds__(256) bvh_emit_kernel(BvhWork W, Meta *meta, TreeArrays T, uint32_t n) {
+  if (meta->error & 2u) return; // the blind level count was too small: the host redoes the step
   const uint32_t nn = W.meta->n_nodes;
   if (nn > W.node_cap || nn > T.capacity) {
     if (blockIdx.x == 0 && threadIdx.x == 0) { meta->error |= 1u; meta->n_nodes = nn; }

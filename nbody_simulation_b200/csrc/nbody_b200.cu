@@ -93,6 +93,8 @@ struct nb_ctx {
   TileArrays tiles{};
   BvhMeta *h_bmeta = nullptr; // pinned mirror of bw.meta
   uint32_t bvh_levels = 0;    // levels of the last build
+  bool bmeta_in_flight = false;  // a copy of BvhMeta into h_bmeta is enqueued: read it after the next synchronisation
+  bool bvh_levels_known = false; // ... from a completed build of this context: the next build is enqueued blind
 
   BodyArrays body[2]{};
   int cur = 0; // body[cur] holds the current state (slot order)
@@ -247,7 +249,19 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
     return level >= 31 ? by_size : std::min(by_size, 1u << level);
   };
   int level = 0;
-  if (n > kBvhSmall) {
+  if (n > kBvhSmall && c->bvh_levels_known) {
+    // No host synchronisation: as many levels as the previous build needed plus one, then a one-thread kernel
+    // checks that no big node is left.  If one is, the rest of the step is a no-op and the host — which sees the flag
+    // at its next look at Meta — redoes the step through the synchronising loop below (do_steps, nb_build_tree).
+    const int blind = std::min((int)c->bvh_levels + 1, kBvhMaxLevels);
+    for (; level < blind; ++level) enqueue_level(level, bound(level));
+    bvh_levels_check_kernel<<<1, 32, 0, st>>>(W, c->meta, blind, c->step_seq);
+    g_launches += 1;
+    // the level count of THIS build reaches the host with the next copy of BvhMeta (sync_and_check)
+    NB_CUDA(c, cudaMemcpyAsync(c->h_bmeta, W.meta, sizeof(BvhMeta), cudaMemcpyDeviceToHost, st));
+    c->bmeta_in_flight = true;
+  } else if (n > kBvhSmall) {
+    // first build of a context (or the redo of a failed guess): look after every level
     for (; level < (int)c->bvh_levels && level < kBvhMaxLevels; ++level) enqueue_level(level, bound(level));
     for (;; ++level) {
       NB_CUDA(c, cudaMemcpyAsync(c->h_bmeta, W.meta, sizeof(BvhMeta), cudaMemcpyDeviceToHost, st));
@@ -260,6 +274,7 @@ int enqueue_build_bvh_ref(nb_ctx *c) {
     int used = 0;
     while (used < kBvhMaxLevels && c->h_bmeta->cnt_big[used] != 0) ++used;
     c->bvh_levels = (uint32_t)used;
+    c->bvh_levels_known = true;
   }
   // everything below: one block per small subtree, in shared memory
   bvh_subtree_kernel<<<kSMs * 2, kSubThreads, sizeof(SubSmem), st>>>(W, (uint32_t)c->leaf_cap);
@@ -482,10 +497,17 @@ int sync_and_check(nb_ctx *c) {
   NB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->meta, sizeof(Meta), cudaMemcpyDeviceToHost, c->stream));
   NB_CUDA(c, cudaStreamSynchronize(c->stream));
   c->resort_hit = false;
+  if (c->bmeta_in_flight) { // NB_TREE_BVH_REF, blind build: how many levels the last build enqueued really needed
+    c->bmeta_in_flight = false;
+    int used = 0;
+    while (used < kBvhMaxLevels && c->h_bmeta->cnt_big[used] != 0) ++used;
+    c->bvh_levels = (uint32_t)used;
+  }
   if (c->h_meta->fail_seq != 0xffffffffu) { // some build since the last check guessed the depth too shallow
     c->resort_hit = true;
     c->resort_at = c->h_meta->fail_seq;
     c->depth_known = false; // the next build sorts every digit
+    c->bvh_levels_known = false; // ... and NB_TREE_BVH_REF looks after every level again
     c->redo_next = true;
     c->redo_guess = c->last_top_passes;
     ++c->resorts;

@@ -238,3 +238,27 @@ def test_bvh_ref_draw_follows_the_permuted_vec_order():
     frame = w.draw().reshape(-1, 4)
     assert np.array_equal(frame, draw_sequential(host))
     w.close()
+
+
+def test_bvh_ref_blind_level_count_is_checked_on_the_device_and_redone():
+    # round 2: after the first build the host enqueues the level-synchronous part blind (previous level count + 1, no
+    # synchronisation); a deeper tree than guessed turns the step into a no-op and the host redoes it.  Same trajectory
+    # as a context that never guessed, including in the middle of an nb_step batch.
+    small, big = scene("disc", 20_000), scene("plummer", 120_000)
+    ref = nb.World(len(big), theta=0.7, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    ref.set_particles(big)
+    ref.step(3)
+    w = nb.World(len(big), theta=0.7, tree=nb.NB_TREE_BVH_REF, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(small)
+    w.step(2)  # few big levels: that count is the next guess
+    w.set_particles(big)
+    c = nb.Counting()
+    w.step(3, c)
+    assert c.steps == 3
+    assert np.array_equal(bits(w.particles), bits(ref.particles))
+    # and back to a shallow scene: the guess overshoots (no-op levels), nothing to redo
+    w.set_particles(small)
+    w.build_tree()
+    assert_bvh_equal(w.tree(), ob.Tree(ob.KIND_LITERAL_BVH, small["x"], small["y"], small["weight"]).export(), "after overshoot")
+    w.close()
+    ref.close()
