@@ -330,7 +330,10 @@ int enqueue_build(nb_ctx *c) {
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
-  const bool reorder = c->aos_fresh && n >= c->aos_permute_min;
+  // Not with the peer exchange: the re-order flips the ping-pong parity, so this step's integrate kernel would push
+  // into the peers' ORIGINAL buffer — which a slower peer may still be reading for its own Morton keys (no hand-shake
+  // separates an upload from the first step).  There the first step pays the caller-order gathers instead.
+  const bool reorder = c->aos_fresh && n >= c->aos_permute_min && !(c->n_ranks > 1 && c->peer);
   c->aos_fresh = false;
   if (reorder) { // first build after an upload: bring the state into tree order once, through the AoS copy
     permute_from_aos_kernel<<<gb_of(n), 256, 0, st>>>(c->aos, order, c->body[c->cur ^ 1], n);
