@@ -32,7 +32,8 @@ FLOP_PER_INTERACTION = 14  # literal count of src/main.rs:235-253 (SURVEY.md §8
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200,
+                    help="timed steps (default 200: a 0.2 s timed region at 1M bodies, so that the clock samples mean something)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-per-gpu", type=int, default=1_000_000)
