@@ -12,10 +12,9 @@
 // Top-digit (speculative) sort.  The tree only needs the bodies ordered down to the deepest leaf: inside a leaf
 // tree_finish_kernel orders them by body id whatever the sort left.  When the previous build's depth is known,
 // radix_sort_pairs runs just the top `top_passes` digits (a stable LSD sort of those digits), tree_count_kernel
-// checks that no leaf is deeper than the sorted prefix, and if one is (meta->resort) the passes that
-// radix_sort_fallback enqueued behind it — every kernel of them a no-op otherwise — sort the permuted pairs by the
-// full key.  A stable full sort of a stably top-sorted permutation is the stable full sort of the input, and the
-// plan has an even number of passes, so either way the result sits in the same buffer.
+// checks that no leaf is deeper than the sorted prefix, and if one is it raises meta->resort / error bit 1: the rest
+// of the step does nothing and the host redoes it with a full sort (do_steps in nbody_b200.cu).  Round 1 enqueued the
+// full sort behind every build as conditional no-op launches instead; that chain (radix_sort_fallback) is gone.
 #pragma once
 #include "common.cuh"
 #include "scan.cuh"
@@ -102,7 +101,6 @@ __global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restric
   if ((int)threadIdx.x < radix) h[threadIdx.x] = ex;
   if (threadIdx.x == 0) {
     tickets[p] = 0;
-    tickets[kSortMaxPasses + 1 + p] = 0; // the fallback passes' tickets
   }
   if (meta && p == plan.passes - 1) {
     if (plan.bits[p] == 9 && threadIdx.x == 256) meta->n_in = ex;
@@ -289,9 +287,9 @@ inline void sort_enqueue_pass(const SortPlan &plan, int p, int rounds, uint32_t 
 #undef NB_SORT_PASS
 }
 
-// True if radix_sort_pairs(..., top_passes) + radix_sort_fallback is usable for this plan (see the header).
+// True if radix_sort_pairs(..., top_passes) may sort only the top digits of this plan (see the header).
 inline bool sort_can_speculate(const SortPlan &plan, int top_passes) {
-  return top_passes > 0 && top_passes < plan.passes && (plan.passes % 2) == 0;
+  return top_passes > 0 && top_passes < plan.passes;
 }
 
 // Sorts the low `bits` key bits — or, with top_passes > 0, only the top `top_passes` digits of them (stable).
@@ -330,31 +328,6 @@ inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsign
     prof_mark(st, "sort_onesweep_kernel");
   }
   return which;
-}
-
-// After radix_sort_pairs(..., top_passes) returned `which`: the full sort, every pass conditional on *cond
-// (= &meta->resort, raised by tree_count_kernel).  The result stays in buffer `which`.
-inline void radix_sort_fallback(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
-                                uint32_t *vals_b, int which, uint32_t n, int bits, int top_passes,
-                                const SortScratch &sc, cudaStream_t st, const uint32_t *cond) {
-  if (n == 0) return;
-  const SortPlan plan = make_sort_plan(bits);
-  if (!sort_can_speculate(plan, top_passes)) return;
-  const int rounds = sort_rounds_for(n);
-  const uint32_t tile_elems = (uint32_t)(kSortThreads * rounds);
-  const uint32_t tiles = (n + tile_elems - 1) / tile_elems;
-  size_t soff = 0;
-  for (int p = plan.passes - top_passes; p < plan.passes; ++p) soff += (size_t)tiles << plan.bits[p];
-  unsigned long long *kin = which ? keys_b : keys_a, *kout = which ? keys_a : keys_b;
-  uint32_t *vin = which ? vals_b : vals_a, *vout = which ? vals_a : vals_b;
-  g_launches += plan.passes;
-  for (int p = 0; p < plan.passes; ++p) {
-    sort_enqueue_pass(plan, p, rounds, tiles, kin, vin, kout, vout, n, sc.ghist + plan.hist_off[p],
-                      sc.tickets + kSortMaxPasses + 1 + p, sc.status + soff, cond, st);
-    soff += (size_t)tiles << plan.bits[p];
-    unsigned long long *tk = kin; kin = kout; kout = tk;
-    uint32_t *tv = vin; vin = vout; vout = tv;
-  }
 }
 
 } // namespace nb
