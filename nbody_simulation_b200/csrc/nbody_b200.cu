@@ -996,6 +996,7 @@ int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) 
   NB_CUDA(c, cudaSetDevice(c->device));
   c->tree_valid = false;
   c->v_partial = false;
+  c->aos_fresh = false; // the staging buffer no longer describes the state
   cudaStream_t st = c->stream;
   int rc;
   if (scene == NB_SCENE_DEFAULT) { // World::new (main.rs:276-346): 2 cores + grid disc + 100 000 rand_body; n is ignored
@@ -1459,6 +1460,7 @@ int nb_load_snapshot(nb_ctx *c, const char *path, uint64_t *steps_done) {
   int rc = nb_set_bodies_aos(c, buf.data(), buf.size());
   if (rc == NB_OK && ver[0] == 2u && (ver[1] & 1u) && !buf.empty()) { // slot-order snapshot: ids from the pad words
     aos_to_soa_kernel<<<cdiv(c->n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], c->n, true);
+    c->aos_fresh = false; // the ids come from the pad words: permute_from_aos_kernel would number the bodies by slot
     NB_CUDA(c, cudaGetLastError());
     NB_CUDA(c, cudaStreamSynchronize(c->stream));
   }

@@ -495,3 +495,29 @@ def test_top_digit_sort_too_shallow_inside_a_batch_of_steps():
     assert np.array_equal(bits(w.particles), bits(ref.particles))
     w.close()
     ref.close()
+
+
+def test_upload_then_device_generation_does_not_reuse_the_stale_upload(monkeypatch):
+    # an AoS upload leaves its records in the staging buffer for the one-pass re-order of the next build (from 2M bodies;
+    # forced on for every size here): any other way of setting the state must drop that claim
+    monkeypatch.setenv("NB_B200_AOS_PERMUTE_MIN", "0")
+    n = 50_000
+    w = nb.World(n, theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(scene("galaxy", n))           # upload: the staging buffer describes this state ...
+    w.generate_on_device(nb.NB_SCENE_UNIFORM_DISC, 1, n)  # ... and no longer this one
+    w.step(2)
+    ref = nb.World(n, theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    ref.generate_on_device(nb.NB_SCENE_UNIFORM_DISC, 1, n)
+    ref.step(2)
+    assert np.array_equal(bits(w.particles), bits(ref.particles))
+    # and the re-order itself: upload + steps equals the resident path
+    p = scene("galaxy", n)
+    w.set_particles(p)
+    w.step(2)
+    monkeypatch.setenv("NB_B200_AOS_PERMUTE_MIN", "4000000000")
+    r2 = nb.World(n, theta=0.5, force_mode=nb.NB_FORCE_EXACT)
+    r2.set_particles(p)
+    r2.step(2)
+    assert np.array_equal(bits(w.particles), bits(r2.particles))
+    for x in (w, ref, r2):
+        x.close()
