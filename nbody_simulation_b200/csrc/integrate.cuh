@@ -152,8 +152,10 @@ __global__ void __launch_bounds__(256) pull_velocity_kernel(BodyArrays b, PeerOu
 
 // nb_world_update_shard: rank r holds bodies [first, first + count) of the caller's Vec.  One kernel splits the AoS
 // records and stores the slice into EVERY rank's state arrays (slot == original index); the u32 weights travel as
-// raw bits through the x array of the other ping-pong buffer (free until the step writes it) and are moved into
-// m[] by unpack_shard_kernel after the hand-shake.
+// raw bits through the VX array of the other ping-pong buffer and are moved into m[] by unpack_shard_kernel after the
+// hand-shake.  vx, not x: the step's integrate kernel pushes positions into the peers' other buffer, and nothing orders a
+// slow rank's unpack before a fast rank's push; velocities are never pushed (integrate_push_kernel), so vx is only
+// written by its owner, after its own unpack in stream order.
 __global__ void __launch_bounds__(256) push_shard_kernel(const float *__restrict__ aos, PeerOut cur, PeerOut other,
                                                          int n_ranks, uint32_t first, uint32_t count) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(256) push_shard_kernel(const float *__restrict
     cur.y[r][i] = p.y;
     cur.vx[r][i] = v.x;
     cur.vy[r][i] = v.y;
-    other.x[r][i] = w;
+    other.vx[r][i] = w;
   }
 }
 __global__ void __launch_bounds__(256) unpack_shard_kernel(BodyArrays b, const float *__restrict__ wbits, uint32_t n) {

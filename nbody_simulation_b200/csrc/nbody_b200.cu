@@ -1161,7 +1161,7 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
     push_shard_kernel<<<cdiv((uint32_t)count, 256), 256, 0, st>>>(c->aos, c->peer_out[c->cur], c->peer_out[c->cur ^ 1],
                                                                  c->n_ranks, (uint32_t)first, (uint32_t)count);
   handshake(); // every rank's slice has arrived everywhere
-  unpack_shard_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->body[c->cur ^ 1].x, c->n);
+  unpack_shard_kernel<<<cdiv(c->n, 256), 256, 0, st>>>(c->body[c->cur], c->body[c->cur ^ 1].vx, c->n);
   g_launches += 2;
   mark(3);
   int rc = do_steps(c, 1, delta, out);
