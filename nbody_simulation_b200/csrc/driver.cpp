@@ -5,7 +5,7 @@
 // writes the headless `draw()` frame (main.rs:41-72) to a file instead.
 //
 //   nbody_driver [--scene default|disc|plummer|galaxy] [--n N] [--steps K] [--theta T] [--dt D]
-//                [--tree quad|lbvh] [--exact] [--ppm out.ppm]
+//                [--tree quad|lbvh|bvhref] [--exact] [--ppm out.ppm]
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -32,7 +32,10 @@ int main(int argc, char **argv) {
     else if (a == "--steps") steps = (unsigned)strtoul(next(), nullptr, 10);
     else if (a == "--theta") theta = strtof(next(), nullptr);
     else if (a == "--dt") dt = strtof(next(), nullptr);
-    else if (a == "--tree") tree = std::string(next()) == "lbvh" ? NB_TREE_LBVH : NB_TREE_QUAD;
+    else if (a == "--tree") {
+      const std::string t = next(); // bvhref = the reference's live tree (mod bvh_tree, main.rs:1), bit for bit
+      tree = t == "lbvh" ? NB_TREE_LBVH : t == "bvhref" ? NB_TREE_BVH_REF : NB_TREE_QUAD;
+    }
     else if (a == "--exact") force = NB_FORCE_EXACT;
     else if (a == "--ppm") ppm = next();
     else { fprintf(stderr, "unknown argument %s\n", a.c_str()); return 2; }
