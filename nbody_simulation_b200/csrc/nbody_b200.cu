@@ -399,9 +399,18 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
   traverse_kernel<EX, CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,          \
                                                           c->cfg.theta, first, count)
 #define NB_TRAVERSE_FAST(CNT)                                                                                     \
-  traverse_fast_kernel<CNT><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, c->sacc,        \
-                                                           first, count)
+  do {                                                                                                            \
+    if (transpose)                                                                                                \
+      traverse_fast_kernel<CNT, true><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody,      \
+                                                                     c->sacc, first, count);                      \
+    else                                                                                                          \
+      traverse_fast_kernel<CNT, false><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody,     \
+                                                                      c->sacc, first, count);                     \
+  } while (0)
   const bool ex = c->cfg.force_mode == NB_FORCE_EXACT;
+  // transposed few-taker leaf path (traverse.cuh): re-orders sums, so not on the reference's own tree; fast_walk_group
+  // == 3 switches it off for A/B runs
+  const bool transpose = !c->bvh_ref && c->cfg.fast_walk_group != 3;
   if (!ex && !c->bvh_ref && c->cfg.fast_walk_group == 2) {
     // hybrid: far field by lane-parallel classification + dense lists, near field by the depth-first walk
     const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);
@@ -410,7 +419,7 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
     else
       traverse_hybrid_kernel<false><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
   } else
-  if (!ex && !c->bvh_ref && c->cfg.fast_walk_group) {
+  if (!ex && !c->bvh_ref && c->cfg.fast_walk_group == 1) {
     // list-then-evaluate group walk (traverse_group.cuh): quadtree and LBVH in NB_FORCE_FAST
     const uint32_t gblocks = cdiv(cdiv(count, 32), (uint32_t)kGrpWarps);
     if (c->counting)

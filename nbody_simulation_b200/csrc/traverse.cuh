@@ -31,6 +31,16 @@ namespace nb {
 // margin over the f32 rounding of d^2 and the product (~3e-7), and covers theta = 0.7 (0.7f^2 = 0.48999998).
 constexpr float kThetaSqNoContains = 0.49f;
 
+// transposed few-taker leaf path of traverse_fast_body: ranges shorter than this stay with the plain loop
+#ifndef NB_TRANSPOSE_MIN_BODIES
+#define NB_TRANSPOSE_MIN_BODIES 6
+#endif
+constexpr uint32_t kTransposeMinBodies = NB_TRANSPOSE_MIN_BODIES;
+#ifndef NB_TRANSPOSE_MAX_TAKERS
+#define NB_TRANSPOSE_MAX_TAKERS 16
+#endif
+constexpr int kTransposeMaxTakers = NB_TRANSPOSE_MAX_TAKERS; // 8: groups of 4 or 8 lanes; 16 adds groups of 2
+
 // main.rs:235-253 with diff = (dx, dy) and d2 = dx*dx + dy*dy already computed.
 template <bool EXACT>
 __device__ __forceinline__ void force_from_diff(float dx, float dy, float d2, float m, float &ax, float &ay) {
@@ -184,12 +194,13 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 //    did not accept the twig) keep the copy — no divergent branch, no per-body predicate or select;
 //  * summation order inside a lane is unchanged (tree order): with ~2e4 interactions per body on the
 //    reference's own tree, any reordering shows up as ~1e-5 of rounding noise against the reference.
-template <bool COUNT, bool CONTAINS>
+template <bool COUNT, bool CONTAINS, bool TRANSPOSE = false>
 __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
                                                    Meta *meta, const float4 *__restrict__ sbody,
                                                    float2 *__restrict__ sacc, const float theta2, uint32_t tfirst,
                                                    uint32_t tcount) {
   const unsigned lane = threadIdx.x & 31;
+  __shared__ unsigned char s_src[TRANSPOSE ? 8 : 1][16]; // transposed leaf path: lane of the q-th taker, per warp
   const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
   if (t0 >= tcount) return;
   const bool valid = (t0 + lane) < tcount;
@@ -234,7 +245,43 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
         n_test += (twig && active) ? 1u : 0u;
         n_inter += (acc ? 1u : 0u) + (take ? k : 0u);
       }
-      if (__any_sync(0xffffffffu, take)) {
+      const unsigned tkm = __ballot_sync(0xffffffffu, take);
+      if (TRANSPOSE && tkm != 0u && __popc(tkm) <= kTransposeMaxTakers && k >= kTransposeMinBodies) {
+        // Few takers (39 % of the leaf-loop trips run with <= 8 of 32 lanes taking, 22 % with <= 4): transpose.  Taker
+        // number q gets a group of 4 lanes (8 when at most 4 lanes take), each lane sums every 4th (8th) body of the
+        // range for it, shuffles reduce the partial sums and one more hands the result back: ceil(k / 4) or
+        // ceil(k / 8) trips instead of k / 2 with most lanes idle.  The partial sums re-order the lane's additions:
+        // FAST mode on the Morton trees only (the reference's own tree keeps the plain loop, see the kernel's header).
+        const unsigned nt = __popc(tkm);
+        const unsigned myq = __popc(tkm & ((1u << lane) - 1u));
+        if (take) s_src[threadIdx.x >> 5][myq] = (unsigned char)lane;
+        __syncwarp();
+        const unsigned sh = nt <= 4u ? 3u : (nt <= 8u ? 2u : 1u); // log2(lanes per taker)
+        const unsigned q = lane >> sh, r = lane & ((1u << sh) - 1u), step = 1u << sh;
+        const unsigned src = q < nt ? s_src[threadIdx.x >> 5][q] : lane;
+        const float2 tp = make_float2(__shfl_sync(0xffffffffu, np.x, src), __shfl_sync(0xffffffffu, np.y, src));
+        float sx = 0.f, sy = 0.f;
+        const float4 *bp = sbody + l.y;
+#pragma unroll 1
+        for (uint32_t j = r; j < k; j += step) {
+          const float4 b0 = bp[j];
+          const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), tp);
+          const float w0 = b0.z * rcp_approx(fmaf(fabsf(e0.x) + fabsf(e0.y), fmaxf(fmaf(e0.y, e0.y, e0.x * e0.x), 0.001f), 1e-20f));
+          sx = fmaf(e0.x, w0, sx); sy = fmaf(e0.y, w0, sy);
+        }
+        sx += __shfl_xor_sync(0xffffffffu, sx, 1); sy += __shfl_xor_sync(0xffffffffu, sy, 1);
+        if (sh >= 2u) { // warp-uniform
+          sx += __shfl_xor_sync(0xffffffffu, sx, 2); sy += __shfl_xor_sync(0xffffffffu, sy, 2);
+        }
+        if (sh == 3u) {
+          sx += __shfl_xor_sync(0xffffffffu, sx, 4); sy += __shfl_xor_sync(0xffffffffu, sy, 4);
+        }
+        const float gx = __shfl_sync(0xffffffffu, sx, (myq << sh) & 31u), gy = __shfl_sync(0xffffffffu, sy, (myq << sh) & 31u);
+        ax = take ? ax + gx : ax;
+        ay = take ? ay + gy : ay;
+        __syncwarp();
+      } else
+      if (tkm != 0u) {
         // warp-uniform trip count; every lane runs the leaf on a copy of its sum and only the takers keep it.
         // Bodies are summed in index order: an odd first body alone, then pairs.  The loop is kept rolled on
         // purpose: leaves hold 4-5 bodies on average, and the dispatch code of an unrolled loop with remainder
@@ -296,7 +343,7 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
 // theta^2 is read from device memory (Meta::theta2, written by the host) rather than passed as a kernel parameter:
 // ptxas re-reads a parameter from the constant bank — or re-multiplies theta * theta — on every node visit, one
 // issue slot each time in a kernel bound by issue slots; a value loaded from global memory stays in its register.
-template <bool COUNT>
+template <bool COUNT, bool TRANSPOSE = false>
 __global__ void __launch_bounds__(256) traverse_fast_kernel(const float4 *__restrict__ box,
                                                             const float4 *__restrict__ node, Meta *meta,
                                                             const float4 *__restrict__ sbody,
@@ -306,9 +353,9 @@ __global__ void __launch_bounds__(256) traverse_fast_kernel(const float4 *__rest
   const float theta2 = meta->theta2;
   // Rectangle::contains is needed unless provably implied (kThetaSqNoContains)
   if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0)
-    traverse_fast_body<COUNT, true>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
+    traverse_fast_body<COUNT, true, TRANSPOSE>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
   else
-    traverse_fast_body<COUNT, false>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
+    traverse_fast_body<COUNT, false, TRANSPOSE>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
 }
 
 } // namespace nb
