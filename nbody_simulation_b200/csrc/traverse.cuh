@@ -261,10 +261,10 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
         const unsigned src = q < nt ? s_src[threadIdx.x >> 5][q] : lane;
         const float2 tp = make_float2(__shfl_sync(0xffffffffu, np.x, src), __shfl_sync(0xffffffffu, np.y, src));
         float sx = 0.f, sy = 0.f;
-        const float4 *bp = sbody + l.y;
+        const float4 *bp = sbody + l.y + r; // a running pointer: one IMAD.WIDE per trip instead of four address instructions
 #pragma unroll 1
-        for (uint32_t j = r; j < k; j += step) {
-          const float4 b0 = bp[j];
+        for (uint32_t j = r; j < k; j += step, bp += step) {
+          const float4 b0 = *bp;
           const float2 e0 = __fadd2_rn(make_float2(b0.x, b0.y), tp);
           const float w0 = b0.z * rcp_approx(fmaf(fabsf(e0.x) + fabsf(e0.y), fmaxf(fmaf(e0.y, e0.y, e0.x * e0.x), 0.001f), 1e-20f));
           sx = fmaf(e0.x, w0, sx); sy = fmaf(e0.y, w0, sy);
