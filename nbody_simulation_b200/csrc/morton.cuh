@@ -10,11 +10,15 @@ namespace nb {
 // child offset = mid (bit set) or offset.  Same f32 midline chain as the reference, so the key
 // is the literal insertion path to any depth; child = (north<<1) + west (quad_tree.rs:179) puts
 // the y bit above the x bit.
+// LEVELS < kQuadLevels: only the top LEVELS levels of the path, the bits below are zero.  The build asks for as many
+// levels as its top-digit sort covers (radix_sort.cuh): a leaf that would need more is caught by tree_count_kernel
+// (equal truncated keys share all 24 levels) and the step is redone with the full chain.
+template <int LEVELS = kQuadLevels>
 __device__ __forceinline__ unsigned long long morton_chain(float px, float py, float x0, float y0, float h) {
   float ox = x0, oy = y0, hh = h;
   unsigned long long key = 0;
 #pragma unroll
-  for (int l = 0; l < kQuadLevels; ++l) {
+  for (int l = 0; l < LEVELS; ++l) {
     hh = __fmul_rn(hh, 0.5f); // == hh / 2.0 exactly
     float mx = __fadd_rn(ox, hh), my = __fadd_rn(oy, hh);
     bool bx = px > mx, by = py > my;
@@ -22,7 +26,7 @@ __device__ __forceinline__ unsigned long long morton_chain(float px, float py, f
     ox = bx ? mx : ox;
     oy = by ? my : oy;
   }
-  return key;
+  return key << (2 * (kQuadLevels - LEVELS));
 }
 
 // The caller-side filter the reference implies for its quadtree (within_bounds, main.rs:223-226).
@@ -30,6 +34,7 @@ __device__ __forceinline__ bool in_domain(float px, float py, float x0, float y0
   return py < __fadd_rn(y0, h) && px < __fadd_rn(x0, h) && py >= y0 && px >= x0;
 }
 
+template <int LEVELS = kQuadLevels>
 __global__ void __launch_bounds__(256) morton_kernel(const float *__restrict__ x, const float *__restrict__ y,
                                                      const Meta *__restrict__ meta, uint32_t n, int quad_mode,
                                                      unsigned long long *__restrict__ keys,
@@ -53,7 +58,7 @@ __global__ void __launch_bounds__(256) morton_kernel(const float *__restrict__ x
   unsigned long long kk[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    kk[k] = morton_chain(px[k], py[k], x0, y0, h);
+    kk[k] = morton_chain<LEVELS>(px[k], py[k], x0, y0, h);
     if (quad_mode && !in_domain(px[k], py[k], x0, y0, h)) kk[k] = kKeyOut;
   }
   if (i4 + 3 < n) {

@@ -323,7 +323,17 @@ int enqueue_build(nb_ctx *c) {
   c->last_redone = c->redo_next;
   c->last_failed_guess = c->redo_guess;
   c->redo_next = false;
-  morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, st>>>(b0.x, b0.y, c->meta, n, c->quad ? 1 : 0, c->keys[0], c->vals[0]);
+  { // only the levels the top-digit sort covers (4 per digit; the check in tree_count_kernel catches a deeper leaf)
+    const uint32_t mg = cdiv(cdiv(n, 4), 256);
+    const int q = c->quad ? 1 : 0;
+    switch (top_passes) {
+    case 2: morton_kernel<8><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    case 3: morton_kernel<12><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    case 4: morton_kernel<16><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    case 5: morton_kernel<20><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    default: morton_kernel<kQuadLevels><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    }
+  }
   prof_mark(st, "morton_kernel");
   const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
                                      c->meta, top_passes);
@@ -1347,7 +1357,7 @@ int nb_get_tree(nb_ctx *c, const nb_tree_view *v) {
     // recompute the slot-order keys into the free ping-pong buffer, then to original order
     unsigned long long *tmp = nullptr;
     NB_CUDA(c, dmalloc(&tmp, (size_t)n));
-    morton_kernel<<<cdiv(cdiv(n, 4), 256), 256, 0, c->stream>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[w ^ 1],
+    morton_kernel<kQuadLevels><<<cdiv(cdiv(n, 4), 256), 256, 0, c->stream>>>(b.x, b.y, c->meta, n, c->quad ? 1 : 0, c->keys[w ^ 1],
                                                                   c->vals[w ^ 1]);
     unpermute_key_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(c->keys[w ^ 1], b.id, n, tmp);
     NB_CUDA(c, cudaGetLastError());
