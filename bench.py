@@ -470,7 +470,7 @@ def main():
     w.build_tree()
     ti = w.tree_info()
     sort_note = ("n/a" if args.tree == "bvhref" else "every key digit" if ti.sort_top_digits == 0 else
-                 f"top {ti.sort_top_digits} of 6 key digits per build, the depth guess checked on the device in every step "
+                 f"{ti.sort_top_digits} passes over the top {ti.sort_top_levels} quadtree levels of the keys per build (a full sort takes 6), the depth guess checked on the device in every step "
                  f"and redone in full when too shallow (last build redone: {bool(ti.sort_redone)}); same tree bit for bit "
                  "as the full sort (tests/test_gpu_parity.py::test_top_digit_sort_*), --full-sort turns it off")
     if clocks is not None:

@@ -78,7 +78,8 @@ class NbTreeInfo(C.Structure):
         ("root_h", C.c_float),
         ("sort_top_digits", C.c_uint32),
         ("sort_redone", C.c_uint32),
-        ("reserved", C.c_uint32 * 3),
+        ("sort_top_levels", C.c_uint32),
+        ("reserved", C.c_uint32 * 2),
     ]
 
 

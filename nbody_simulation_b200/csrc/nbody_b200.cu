@@ -118,6 +118,7 @@ struct nb_ctx {
   uint32_t last_max_depth = 0; // deepest leaf of the last checked build: sizes the next step's top-digit sort
   uint32_t resorts = 0;        // builds (as seen at the checks) whose top-digit sort had to be redone in full
   int last_top_passes = 0;     // top digits the last build sorted before checking (0 = full sort)
+  int last_top_levels = 0;     // ... and the quadtree levels they cover
   bool counting = true; // interaction / opening-test counters in the traversal
   unsigned long long seen_interactions = 0, seen_tests = 0;
   uint32_t step_seq = 0;       // sequence number of the build being enqueued (tree_count_kernel -> Meta::fail_seq)
@@ -125,6 +126,7 @@ struct nb_ctx {
   uint32_t resort_at = 0;      // ... and this is its sequence number
   bool redo_next = false, last_redone = false; // the next / the last build is the full-sort redo of a failed guess
   int redo_guess = 0, last_failed_guess = 0;   // the guess that failed
+  int redo_guess_levels = 0, last_failed_levels = 0;
 
   std::vector<cudaEvent_t> ev; // 5 per timed step, drained in batches
   size_t ev_used = 0;
@@ -310,33 +312,42 @@ int enqueue_build(nb_ctx *c) {
     bounds_final_kernel<<<1, 32, 0, st>>>(c->bounds_partial, np, c->meta);
   }
   g_launches += 5; // morton, count, block-base scan, emit, finish (+ the sort, counted there; + link, counted below)
-  // Quadtree: sort only as many top digits as the previous build's depth (+1 level) needs; tree_count_kernel
-  // verifies, and the host redoes the step with a full sort if the guess was too shallow (radix_sort.cuh).  Digit p
-  // from the top covers 4 quadtree levels (the top digit also holds the outside bit).
-  int top_passes = 0;
+  // Quadtree: sort only as many top key bits as the previous build's depth (+1 level) needs, in as few passes as
+  // digits of up to 9 bits allow; tree_count_kernel verifies, and the host redoes the step with a full sort if the
+  // guess was too shallow (radix_sort.cuh).  The top bit of the key is the outside bit, two bits per level below it.
+  SortPlan plan = make_sort_plan(c->quad ? 49 : 48);
+  int top_passes = 0, sorted_levels = 0;
   if (c->quad && c->depth_known && !c->cfg.full_sort) {
-    const int want = ((int)c->last_max_depth + 1 + 3) / 4;
-    top_passes = want < 2 ? 2 : want;
-    if (!sort_can_speculate(make_sort_plan(49), top_passes)) top_passes = 0;
-  }
-  c->last_top_passes = top_passes;
-  c->last_redone = c->redo_next;
-  c->last_failed_guess = c->redo_guess;
-  c->redo_next = false;
-  { // only the levels the top-digit sort covers (4 per digit; the check in tree_count_kernel catches a deeper leaf)
-    const uint32_t mg = cdiv(cdiv(n, 4), 256);
-    const int q = c->quad ? 1 : 0;
-    switch (top_passes) {
-    case 2: morton_kernel<8><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
-    case 3: morton_kernel<12><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
-    case 4: morton_kernel<16><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
-    case 5: morton_kernel<20><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
-    default: morton_kernel<kQuadLevels><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0]); break;
+    const int levels = std::max((int)c->last_max_depth + 1, 8);
+    const SortPlan top = make_top_plan(49, 2 * levels + 1);
+    if (top.passes < plan.passes) {
+      plan = top;
+      top_passes = top.passes;
+      sorted_levels = (top.sorted_bits - 1) / 2;
     }
   }
+  c->last_top_passes = top_passes;
+  c->last_top_levels = sorted_levels;
+  c->last_redone = c->redo_next;
+  c->last_failed_guess = c->redo_guess;
+  c->last_failed_levels = c->redo_guess_levels;
+  c->redo_next = false;
+  { // only the levels the top-digit sort covers (the check in tree_count_kernel catches a deeper leaf)
+    const uint32_t mg = cdiv(cdiv(n, 4), 256);
+    const int q = c->quad ? 1 : 0;
+#define NB_MORTON(L) morton_kernel<L><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0])
+    if (sorted_levels == 0 || sorted_levels > 20) NB_MORTON(kQuadLevels);
+    else if (sorted_levels <= 8) NB_MORTON(8);
+    else if (sorted_levels <= 10) NB_MORTON(10);
+    else if (sorted_levels <= 12) NB_MORTON(12);
+    else if (sorted_levels <= 13) NB_MORTON(13);
+    else if (sorted_levels <= 14) NB_MORTON(14);
+    else if (sorted_levels <= 16) NB_MORTON(16);
+    else NB_MORTON(20);
+#undef NB_MORTON
+  }
   prof_mark(st, "morton_kernel");
-  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, c->quad ? 49 : 48, c->sort, st,
-                                     c->meta, top_passes);
+  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, plan, c->sort, st, c->meta);
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
@@ -355,7 +366,7 @@ int enqueue_build(nb_ctx *c) {
   const uint32_t gb = cdiv(n, 256);
   uint32_t *bbase = c->sort.bsum; // per-256-body block: node count, then (scan_bsum_kernel) the block's first node index
   if (c->quad)
-    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, 4 * top_passes, c->step_seq);
+    tree_count_kernel<2, false><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase, sorted_levels, c->step_seq);
   else tree_count_kernel<1, true><<<gb, 256, 0, st>>>(skeys, c->meta, c->leaf_cap, c->leafdepth, c->nstart, bbase);
   prof_mark(st, "tree_count_kernel");
   { // block bases + meta->n_nodes: chunks of 1024 block totals, then their bases (scan.cuh)
@@ -532,6 +543,7 @@ int sync_and_check(nb_ctx *c) {
     c->bvh_levels_known = false; // ... and NB_TREE_BVH_REF looks after every level again
     c->redo_next = true;
     c->redo_guess = c->last_top_passes;
+    c->redo_guess_levels = c->last_top_levels;
     ++c->resorts;
     NB_CUDA(c, cudaMemsetAsync(&c->meta->fail_seq, 0xff, sizeof(uint32_t), c->stream));
     NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), c->stream));
@@ -1339,6 +1351,7 @@ int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {
   info->overflow_leaves = c->n ? m.overflow_leaves : 0;
   info->root_x0 = m.x0; info->root_y0 = m.y0; info->root_h = m.h;
   info->sort_top_digits = c->n ? (uint32_t)(c->last_redone ? c->last_failed_guess : c->last_top_passes) : 0;
+  info->sort_top_levels = c->n ? (uint32_t)(c->last_redone ? c->last_failed_levels : c->last_top_levels) : 0;
   info->sort_redone = (c->n && c->last_redone) ? 1u : 0u;
   return NB_OK;
 }

@@ -38,22 +38,52 @@ struct SortPlan { // digit layout of one sort, passed by value to the kernels
   int bits[kSortMaxPasses];
   int hist_off[kSortMaxPasses]; // offset of the pass's bins in the histogram arrays
   int hist_total;
+  int out_bin;      // quadtree keys (odd key_bits): first bin of the top digit with the "outside the root" bit set; else -1
+  int sorted_bits;  // key bits, from the top, that the passes cover (== key_bits for a full sort)
 };
+
+inline void sort_plan_push(SortPlan &p, int shift, int b) {
+  p.shift[p.passes] = shift;
+  p.bits[p.passes] = b;
+  p.hist_off[p.passes] = p.hist_total;
+  p.hist_total += 1 << b;
+  ++p.passes;
+}
 
 inline SortPlan make_sort_plan(int key_bits) { // 8-bit digits; a 9-bit last digit absorbs an odd top bit
   SortPlan p{};
-  int shift = 0, off = 0;
+  int shift = 0;
   while (shift < key_bits) {
     int b = (key_bits - shift == 9) ? 9 : 8;
     if (key_bits - shift < 8) b = key_bits - shift;
-    p.shift[p.passes] = shift;
-    p.bits[p.passes] = b;
-    p.hist_off[p.passes] = off;
-    off += 1 << b;
+    sort_plan_push(p, shift, b);
     shift += b;
-    ++p.passes;
   }
-  p.hist_total = off;
+  p.out_bin = (key_bits & 1) ? 1 << (p.bits[p.passes - 1] - 1) : -1;
+  p.sorted_bits = key_bits;
+  return p;
+}
+
+// Top-digit plan: the fewest passes of at most kSortMaxDigitBits-bit digits that cover the top `top_bits` bits of the
+// key (at least 8 bits per digit, so the plan may cover a few more; the wider digits at the top).  Falls back to the
+// full plan when that is no shorter.
+constexpr int kSortMaxDigitBits = 9;
+inline SortPlan make_top_plan(int key_bits, int top_bits) {
+  const SortPlan full = make_sort_plan(key_bits);
+  if (top_bits <= 0) return full;
+  const int passes = (top_bits + kSortMaxDigitBits - 1) / kSortMaxDigitBits;
+  const int cover = top_bits > 8 * passes ? top_bits : 8 * passes;
+  if (passes >= full.passes || cover >= key_bits) return full;
+  SortPlan p{};
+  const int base = cover / passes, extra = cover % passes;
+  int shift = key_bits - cover;
+  for (int i = 0; i < passes; ++i) {
+    const int b = base + (i >= passes - extra ? 1 : 0);
+    sort_plan_push(p, shift, b);
+    shift += b;
+  }
+  p.out_bin = (key_bits & 1) ? 1 << (p.bits[p.passes - 1] - 1) : -1;
+  p.sorted_bits = cover;
   return p;
 }
 
@@ -89,7 +119,8 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long
 
 // Exclusive scan per pass (one block per pass); also resets the tile tickets.  The last pass of a
 // 49-bit (quadtree) sort has bit 48 = "outside the root square" as its top digit bit, so its exclusive
-// prefix at bin 256 IS the number of bodies in the tree: the per-step metadata is initialised here.
+// prefix at that bit's first bin (SortPlan::out_bin) IS the number of bodies in the tree: the per-step metadata is
+// initialised here.
 __global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restrict__ ghist, SortPlan plan,
                                                              uint32_t *__restrict__ tickets, Meta *meta, uint32_t n) {
   const int p = blockIdx.x;
@@ -103,9 +134,9 @@ __global__ void __launch_bounds__(512) sort_scan_hist_kernel(uint32_t *__restric
     tickets[p] = 0;
   }
   if (meta && p == plan.passes - 1) {
-    if (plan.bits[p] == 9 && threadIdx.x == 256) meta->n_in = ex;
+    if ((int)threadIdx.x == plan.out_bin) meta->n_in = ex;
     if (threadIdx.x == 0) {
-      if (plan.bits[p] != 9) meta->n_in = n;
+      if (plan.out_bin < 0) meta->n_in = n;
       meta->n = n;
       meta->n_nodes = 0;
       meta->n_leaves = 0;
@@ -287,23 +318,16 @@ inline void sort_enqueue_pass(const SortPlan &plan, int p, int rounds, uint32_t 
 #undef NB_SORT_PASS
 }
 
-// True if radix_sort_pairs(..., top_passes) may sort only the top digits of this plan (see the header).
-inline bool sort_can_speculate(const SortPlan &plan, int top_passes) {
-  return top_passes > 0 && top_passes < plan.passes;
-}
-
-// Sorts the low `bits` key bits — or, with top_passes > 0, only the top `top_passes` digits of them (stable).
+// Sorts by the digits of `plan` (stable LSD): make_sort_plan = the whole key, make_top_plan = its top bits only.
 // Returns 0 if the result is in (keys_a, vals_a), 1 if in (keys_b, vals_b).
 inline int radix_sort_pairs(unsigned long long *keys_a, uint32_t *vals_a, unsigned long long *keys_b,
-                            uint32_t *vals_b, uint32_t n, int bits, const SortScratch &sc, cudaStream_t st,
-                            Meta *meta = nullptr, int top_passes = 0) {
+                            uint32_t *vals_b, uint32_t n, const SortPlan &plan, const SortScratch &sc, cudaStream_t st,
+                            Meta *meta = nullptr) {
   if (n == 0) return 0;
-  const SortPlan plan = make_sort_plan(bits);
   const int rounds = sort_rounds_for(n);
   const uint32_t tile_elems = (uint32_t)(kSortThreads * rounds);
   const uint32_t tiles = (n + tile_elems - 1) / tile_elems;
-  const bool spec = sort_can_speculate(plan, top_passes);
-  const int first = spec ? plan.passes - top_passes : 0;
+  const int first = 0;
   size_t need = 0;
   for (int p = first; p < plan.passes; ++p) need += (size_t)tiles << plan.bits[p];
   cudaMemsetAsync(sc.ghist, 0, plan.hist_total * sizeof(uint32_t), st);

@@ -351,8 +351,14 @@ def test_top_digit_sort_builds_the_same_tree(sc, n):
     w.set_particles(p)
     w.build_tree()
     info = w.tree_info()
-    want = max(2, (first.max_depth + 1 + 3) // 4)  # 4 quadtree levels per key digit, one level of margin
-    assert info.sort_top_digits == (want if want < 6 else 0) and info.sort_redone == 0, (want, info.sort_top_digits)
+    # one level of margin, two key bits per level below the outside bit, digits of 8 or 9 bits (make_top_plan)
+    bits_needed = 2 * max(first.max_depth + 1, 8) + 1
+    want = -(-bits_needed // 9)
+    cover = max(bits_needed, 8 * want)
+    if want >= 6 or cover >= 49:
+        want, cover = 0, 1
+    assert info.sort_top_digits == want and info.sort_top_levels == (cover - 1) // 2 and info.sort_redone == 0, \
+        (want, cover, info.sort_top_digits, info.sort_top_levels)
     assert_tree_equal(w.tree(), o, f"{sc}/top-digit sort")
     f = nb.World(len(p), full_sort=True)
     f.set_particles(p)
@@ -375,7 +381,7 @@ def test_top_digit_sort_falls_back_when_the_guess_is_too_shallow():
     c = nb.Counting()
     ax, ay = w.accel(c)
     info = w.tree_info()
-    assert info.max_depth > 4 * info.sort_top_digits >= d0, (d0, info.sort_top_digits, info.max_depth)
+    assert info.max_depth > info.sort_top_levels >= d0, (d0, info.sort_top_levels, info.max_depth)
     assert info.sort_redone == 1
     T = ob.Tree(ob.KIND_PIPE_QUAD, deep["x"], deep["y"], deep["weight"])
     assert_tree_equal(w.tree(), T.export(), "fallback to the full sort")
@@ -385,7 +391,7 @@ def test_top_digit_sort_falls_back_when_the_guess_is_too_shallow():
     w.set_particles(deep)  # now the depth is known: the guess holds
     w.build_tree()
     info = w.tree_info()
-    assert info.sort_redone == 0 and info.sort_top_digits * 4 >= info.max_depth
+    assert info.sort_redone == 0 and info.sort_top_levels >= info.max_depth
     assert_tree_equal(w.tree(), T.export(), "after the fallback")
     w.close()
 
