@@ -139,6 +139,36 @@ __global__ void __launch_bounds__(256) integrate_push_kernel(const uint32_t *__r
   out.id[j] = in.id[s];
 }
 
+// The same integrate + push as the tail of the traversal kernel (traverse.cuh, FUSE): a warp integrates its 32 bodies
+// the moment their walk ends and stores the new positions into every rank's arrays, so the slice crosses NVLink while
+// the other warps are still walking the tree — the exchange hides behind the traversal instead of following it.
+// Same arithmetic, same stores as integrate_push_kernel; `bad` = failed build (carry the state over unchanged).
+struct FuseArgs {
+  const uint32_t *order;
+  BodyArrays in, out;
+  PeerOut pin, po;
+  int n_ranks;
+  uint32_t per;
+  float dt;
+};
+__device__ __forceinline__ void integrate_push_body(const FuseArgs &f, uint32_t j, float2 a, bool bad) {
+  const uint32_t s = bad ? j : f.order[j];
+  const int o = min((int)(s / f.per), f.n_ranks - 1);
+  const float vx0 = f.pin.vx[o][s], vy0 = f.pin.vy[o][s];
+  const float vx = bad ? vx0 : __fadd_rn(vx0, __fmul_rn(a.x, f.dt));
+  const float vy = bad ? vy0 : __fadd_rn(vy0, __fmul_rn(a.y, f.dt));
+  const float x = bad ? f.in.x[s] : __fadd_rn(f.in.x[s], __fmul_rn(vx, f.dt));
+  const float y = bad ? f.in.y[s] : __fadd_rn(f.in.y[s], __fmul_rn(vy, f.dt));
+  for (int r = 0; r < f.n_ranks; ++r) {
+    f.po.x[r][j] = x;
+    f.po.y[r][j] = y;
+  }
+  f.out.vx[j] = vx;
+  f.out.vy[j] = vy;
+  f.out.m[j] = f.in.m[s];
+  f.out.id[j] = f.in.id[s];
+}
+
 // Make the velocities of ALL slots valid on this rank again (after steps whose exchange pushed positions only).
 __global__ void __launch_bounds__(256) pull_velocity_kernel(BodyArrays b, PeerOut pcur, int n_ranks, int rank,
                                                             uint32_t per, uint32_t n) {

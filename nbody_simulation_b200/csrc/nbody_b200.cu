@@ -84,6 +84,8 @@ struct nb_ctx {
   nb_config cfg{};
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;           // multi-GPU: the mass / id re-order of the other ranks' slots runs beside the traversal
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   uint32_t n = 0;       // bodies set
   uint32_t n_alloc = 0; // array capacity (padded)
   int leaf_cap = 8;
@@ -142,6 +144,8 @@ struct nb_ctx {
   uint32_t peer_epoch = 0;
   bool aos_fresh = false;         // c->aos holds the uploaded records of the CURRENT state (caller order == slot order)
   uint32_t aos_permute_min = 1u << 21; // bodies from which the first build after an upload re-orders through the AoS copy
+  int sort_min_levels = 8;        // NB_B200_SORT_MIN_LEVELS: least depth a top-digit sort covers (tests: reach every digit width)
+  bool no_fuse = false;           // NB_B200_NO_FUSE=1: keep integrate + push a kernel of its own (A/B runs)
   bool v_partial = false;         // peer exchange: only the velocities of the owned slots are valid here (integrate.cuh)
   std::vector<void *> peer_mapped; // pointers to close in nb_destroy
 
@@ -318,7 +322,7 @@ int enqueue_build(nb_ctx *c) {
   SortPlan plan = make_sort_plan(c->quad ? 49 : 48);
   int top_passes = 0, sorted_levels = 0;
   if (c->quad && c->depth_known && !c->cfg.full_sort) {
-    const int levels = std::max((int)c->last_max_depth + 1, 8);
+    const int levels = std::max((int)c->last_max_depth + 1, c->sort_min_levels);
     const SortPlan top = make_top_plan(49, 2 * levels + 1);
     if (top.passes < plan.passes) {
       plan = top;
@@ -410,7 +414,32 @@ int enqueue_build(nb_ctx *c) {
 
 // World::bvh_sum_gravity over the par_iter (main.rs:349-386, 406-416) for tree positions
 // [first, first+count).
-int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
+// True if this step's traversal kernel may integrate and push its bodies itself (traverse_fast_push_kernel): the
+// multi-GPU step with the peer mappings, on the default walk of NB_FORCE_FAST.
+bool step_can_fuse(const nb_ctx *c) {
+  return c->n_ranks > 1 && c->peer && c->cfg.force_mode != NB_FORCE_EXACT && !c->bvh_ref &&
+         c->cfg.fast_walk_group == 0 && !c->cfg.faithful_index_bug && !c->no_fuse;
+}
+
+FuseArgs make_fuse_args(nb_ctx *c, float dt) {
+  FuseArgs f{};
+  f.order = c->vals[c->sorted_in];
+  f.in = c->body[c->cur];
+  f.out = c->body[c->cur ^ 1];
+  // Where the velocities are read from: the owners' arrays — except right after an upload / pull, when every
+  // rank holds all of them itself and a peer may not even have finished ITS upload yet (no hand-shake between
+  // an upload and the first step): then, and only then, the local arrays.
+  f.pin = c->peer_out[c->cur];
+  if (!c->v_partial)
+    for (int r = 0; r < kMaxPeers; ++r) { f.pin.vx[r] = f.in.vx; f.pin.vy[r] = f.in.vy; }
+  f.po = c->peer_out[c->cur ^ 1];
+  f.n_ranks = c->n_ranks;
+  f.per = shard_per(c);
+  f.dt = dt;
+  return f;
+}
+
+int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count, const FuseArgs *fuse = nullptr) {
   if (count == 0) return NB_OK;
   const int tpb = 256; // 64 / 128 measured slower (0.84 / 0.83 vs 0.80 ms at 1M); persistent warps with a
                        // global work ticket also measured slower (0.84 ms: consecutive groups lose their shared L1)
@@ -448,6 +477,12 @@ int enqueue_traverse(nb_ctx *c, uint32_t first, uint32_t count) {
     else
       traverse_group_kernel<false><<<gblocks, kGrpWarps * 32, 0, c->stream>>>(c->T.box, c->T.node, c->T.kids, c->meta, c->sbody, c->sacc, first, count);
   } else
+  if (fuse) {
+    if (c->counting)
+      traverse_fast_push_kernel<true><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, first, count, *fuse);
+    else
+      traverse_fast_push_kernel<false><<<blocks, tpb, 0, c->stream>>>(c->T.box, c->T.node, c->meta, c->sbody, first, count, *fuse);
+  } else
   if (ex && c->counting) NB_TRAVERSE(true, true);
   else if (ex) NB_TRAVERSE(true, false);
   else if (c->counting) NB_TRAVERSE_FAST(true);
@@ -465,14 +500,14 @@ int nccl_fail(nb_ctx *c, ncclResult_t r, const char *what) {
 
 // integrate (main.rs:419-423) fused with the physical re-order; multi-GPU: the slices are pushed to the peers
 // by the integrate kernel itself (nb_comm_peer_import) or all-gathered by NCCL afterwards.
-int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
+int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate, bool fused = false, bool permuted = false) {
   const uint32_t n = c->n;
   if (n == 0) return NB_OK;
   uint32_t first, count;
   owned_range(c, first, count);
   BodyArrays &in = c->body[c->cur], &out = c->body[c->cur ^ 1];
   const uint32_t *order = c->vals[c->sorted_in];
-  g_launches += (count ? 1 : 0) + (c->n_ranks > 1 ? 1 : 0);
+  g_launches += (count && !fused ? 1 : 0) + (c->n_ranks > 1 ? 1 : 0);
   if (c->cfg.faithful_index_bug && count) { // single GPU, NB_TREE_BVH_REF (checked in nb_create / nb_comm_init)
     uint32_t *pos_of_slot = c->vals[c->sorted_in ^ 1];
     invert_order_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, n, pos_of_slot);
@@ -481,28 +516,24 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate) {
   } else if (count && !(c->n_ranks > 1 && c->peer))
     integrate_resort_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, first, count, dt, c->meta);
   if (c->n_ranks > 1 && c->peer) {
-    // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here
-    if (count)
-    {
-      // Where the velocities are read from: the owners' arrays — except right after an upload / pull, when every
-      // rank holds all of them itself and a peer may not even have finished ITS upload yet (no hand-shake between
-      // an upload and the first step): then, and only then, the local arrays.
-      PeerOut pin = c->peer_out[c->cur];
-      if (!c->v_partial)
-        for (int r = 0; r < kMaxPeers; ++r) { pin.vx[r] = in.vx; pin.vy[r] = in.vy; }
-      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, pin,
-                                                                    c->peer_out[c->cur ^ 1], c->n_ranks, shard_per(c),
-                                                                    first, count, dt, c->meta);
+    // integrate + exchange in one kernel: every rank's copy of the output slice is stored from here (unless the
+    // traversal kernel did it already: traverse_fast_push_kernel)
+    if (count && !fused) {
+      const FuseArgs f = make_fuse_args(c, dt);
+      integrate_push_kernel<<<cdiv(count, 256), 256, 0, c->stream>>>(order, c->sacc, in, out, f.pin, f.po, c->n_ranks,
+                                                                    f.per, first, count, dt, c->meta);
     }
     c->v_partial = true;
-    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
+    if (permuted) NB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    else permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
     ++c->peer_epoch;
     g_launches += 2;
     peer_signal_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags_of, c->n_ranks, c->rank, c->peer_epoch);
     peer_wait_kernel<<<1, 32, 0, c->stream>>>(c->peer_flags, c->n_ranks, c->peer_epoch, c->meta);
   } else if (c->n_ranks > 1) {
-    permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
+    if (permuted) NB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    else permute_mid_kernel<<<cdiv(n, 256), 256, 0, c->stream>>>(order, in, out, n, first, count, c->meta);
     if (ev_after_integrate) NB_CUDA(c, cudaEventRecord(ev_after_integrate, c->stream));
     const size_t per = (size_t)cdiv(cdiv(n, (uint32_t)c->n_ranks), 32u) * 32u; // == nb_shard_range
     ncclResult_t r;
@@ -619,9 +650,22 @@ int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
       if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
       uint32_t first, count;
       owned_range(c, first, count);
-      if ((rc = enqueue_traverse(c, first, count)) != NB_OK) return rc;
+      // multi-GPU: the masses / ids of the slots other ranks integrate are re-ordered here (every rank knows the order),
+      // on a second stream beside the traversal — memory-bound work next to an issue-bound kernel
+      const bool permuted = c->n_ranks > 1 && !c->cfg.faithful_index_bug && !c->no_fuse;
+      if (permuted) {
+        NB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+        NB_CUDA(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+        permute_mid_kernel<<<cdiv(c->n, 256), 256, 0, c->side>>>(c->vals[c->sorted_in], c->body[c->cur], c->body[c->cur ^ 1], c->n,
+                                                                 first, count, c->meta);
+        NB_CUDA(c, cudaEventRecord(c->ev_join, c->side));
+      }
+      const bool fused = count != 0 && step_can_fuse(c);
+      FuseArgs fa{};
+      if (fused) fa = make_fuse_args(c, dt);
+      if ((rc = enqueue_traverse(c, first, count, fused ? &fa : nullptr)) != NB_OK) return rc;
       if (out) NB_CUDA(c, cudaEventRecord(e2, c->stream));
-      if ((rc = enqueue_integrate(c, dt, e3)) != NB_OK) return rc;
+      if ((rc = enqueue_integrate(c, dt, e3, fused, permuted)) != NB_OK) return rc;
       if (out) NB_CUDA(c, cudaEventRecord(e4, c->stream));
     }
     if ((rc = sync_and_check(c)) != NB_OK) return rc;
@@ -756,6 +800,9 @@ void nb_destroy(nb_ctx *c) {
     cudaFree(c->tiles.sum[i]); cudaFree(c->tiles.guess[i]);
   }
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->side) cudaStreamDestroy(c->side);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -796,6 +843,8 @@ nb_ctx *nb_create(const nb_config *cfg) {
   nb_ctx *c = new nb_ctx();
   c->cfg = *cfg;
   c->device = cfg->device;
+  if (const char *e = std::getenv("NB_B200_NO_FUSE")) c->no_fuse = e[0] == '1';
+  if (const char *e = std::getenv("NB_B200_SORT_MIN_LEVELS")) c->sort_min_levels = std::min(24, std::max(8, std::atoi(e)));
   if (const char *e = std::getenv("NB_B200_AOS_PERMUTE_MIN")) c->aos_permute_min = (uint32_t)std::strtoul(e, nullptr, 10);
   c->quad = cfg->tree_kind == NB_TREE_QUAD;
   c->bvh_ref = cfg->tree_kind == NB_TREE_BVH_REF;
@@ -810,6 +859,9 @@ nb_ctx *nb_create(const nb_config *cfg) {
   if ((e = (call)) != cudaSuccess) return bail(#call, e)
   NB_TRY(cudaSetDevice(c->device));
   NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  NB_TRY(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+  NB_TRY(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  NB_TRY(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   const size_t na = ((size_t)cfg->n_max + 64 + 32 * kMaxPeers + 1023) / 1024 * 1024; // + the all-gather's rounded-up slices
   c->n_alloc = (uint32_t)na;
   for (int i = 0; i < 2; ++i) {
@@ -820,7 +872,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   NB_TRY(dmalloc(&c->leafdepth, na));
   NB_TRY(dmalloc(&c->nstart, na));
   c->sort.status_words = sort_status_words((uint32_t)na);
-  NB_TRY(dmalloc(&c->sort.ghist, (size_t)4096));
+  NB_TRY(dmalloc(&c->sort.ghist, (size_t)8192));
   NB_TRY(dmalloc(&c->sort.tickets, (size_t)16));
   NB_TRY(dmalloc(&c->sort.status, c->sort.status_words));
   NB_TRY(dmalloc(&c->sort.bsum, na / 256 + na / 262144 + 64)); // block totals of tree_count_kernel (256 bodies) / of the flag scan

@@ -66,7 +66,10 @@ inline SortPlan make_sort_plan(int key_bits) { // 8-bit digits; a 9-bit last dig
 
 // Top-digit plan: the fewest passes of at most kSortMaxDigitBits-bit digits that cover the top `top_bits` bits of the
 // key (at least 8 bits per digit, so the plan may cover a few more; the wider digits at the top).  Falls back to the
-// full plan when that is no shorter.
+// full plan when that is no shorter.  9 bits at most: 10-bit digits were built and measured in round 2 (counters and
+// staging buffer sharing their bytes, four digits per thread in the look-back) and dropped — a 1024-bin pass over
+// 4096-pair tiles scatters runs of 4 pairs and costs 1.3x an 8-bit pass: build phase at 8M bodies 1.146 vs 1.166 ms
+// (3 passes instead of 4), at 64M Plummer 9.19 vs 8.52 ms (4 instead of 5).
 constexpr int kSortMaxDigitBits = 9;
 inline SortPlan make_top_plan(int key_bits, int top_bits) {
   const SortPlan full = make_sort_plan(key_bits);

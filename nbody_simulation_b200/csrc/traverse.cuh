@@ -20,6 +20,7 @@
 //  * the interaction / opening-test counters are compiled out unless asked for.
 #pragma once
 #include "common.cuh"
+#include "integrate.cuh"
 #include "tree_build.cuh"
 
 namespace nb {
@@ -194,11 +195,11 @@ __global__ void __launch_bounds__(256) traverse_kernel(const float4 *__restrict_
 //    did not accept the twig) keep the copy — no divergent branch, no per-body predicate or select;
 //  * summation order inside a lane is unchanged (tree order): with ~2e4 interactions per body on the
 //    reference's own tree, any reordering shows up as ~1e-5 of rounding noise against the reference.
-template <bool COUNT, bool CONTAINS, bool TRANSPOSE = false>
+template <bool COUNT, bool CONTAINS, bool TRANSPOSE = false, bool FUSE = false>
 __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ box, const float4 *__restrict__ node,
                                                    Meta *meta, const float4 *__restrict__ sbody,
                                                    float2 *__restrict__ sacc, const float theta2, uint32_t tfirst,
-                                                   uint32_t tcount) {
+                                                   uint32_t tcount, const FuseArgs *fuse = nullptr) {
   const unsigned lane = threadIdx.x & 31;
   __shared__ unsigned char s_src[TRANSPOSE ? 8 : 1][16]; // transposed leaf path: lane of the q-th taker, per warp
   const uint32_t t0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u;
@@ -325,7 +326,9 @@ __device__ __forceinline__ void traverse_fast_body(const float4 *__restrict__ bo
       cur = __any_sync(0xffffffffu, active && !far) ? cur + 1 : l.x;
     }
   }
-  if (valid) sacc[t] = make_float2(ax, ay);
+  if (FUSE) {
+    if (valid) integrate_push_body(*fuse, t, make_float2(ax, ay), false); // multi-GPU: integrate.cuh
+  } else if (valid) sacc[t] = make_float2(ax, ay);
   if (COUNT) {
     unsigned long long wi = n_inter, wt = n_test;
 #pragma unroll
@@ -356,6 +359,25 @@ __global__ void __launch_bounds__(256) traverse_fast_kernel(const float4 *__rest
     traverse_fast_body<COUNT, true, TRANSPOSE>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
   else
     traverse_fast_body<COUNT, false, TRANSPOSE>(box, node, meta, sbody, sacc, theta2, tfirst, tcount);
+}
+
+// Multi-GPU step with the peer mappings: the walk, then integrate + NVLink push of the warp's bodies in the same
+// kernel (integrate_push_body).  A failed build still has to carry the state over, as integrate_push_kernel does.
+template <bool COUNT>
+__global__ void __launch_bounds__(256) traverse_fast_push_kernel(const float4 *__restrict__ box,
+                                                                 const float4 *__restrict__ node, Meta *meta,
+                                                                 const float4 *__restrict__ sbody, uint32_t tfirst,
+                                                                 uint32_t tcount, const __grid_constant__ FuseArgs fuse) {
+  if (meta->error) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < tcount) integrate_push_body(fuse, tfirst + k, make_float2(0.f, 0.f), true);
+    return;
+  }
+  const float theta2 = meta->theta2;
+  if (!(theta2 <= kThetaSqNoContains) || meta->cog_outside != 0)
+    traverse_fast_body<COUNT, true, true, true>(box, node, meta, sbody, nullptr, theta2, tfirst, tcount, &fuse);
+  else
+    traverse_fast_body<COUNT, false, true, true>(box, node, meta, sbody, nullptr, theta2, tfirst, tcount, &fuse);
 }
 
 } // namespace nb

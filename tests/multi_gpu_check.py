@@ -92,6 +92,38 @@ def main():
         ok = ok and same and same2
         w.close()
         ref.close()
+    # ---- the fused step (traverse_fast_push_kernel: walk + integrate + NVLink push in one kernel), including a depth
+    # guess that fails inside a batch of steps (the kernel then carries the state over and the host redoes the steps)
+    for tree in (nb.NB_TREE_QUAD, nb.NB_TREE_LBVH):
+        shallow = nb.generate_scene(nb.NB_SCENE_UNIFORM_DISC, 5, 20_000)
+        deep = nb.generate_scene(nb.NB_SCENE_PLUMMER, 6, 150_001)
+        res = []
+        for multi in (True, False):
+            w = nb.World(len(deep), theta=0.5, dt=0.1, tree=tree, force_mode=nb.NB_FORCE_FAST, device=local)
+            if multi:
+                uid = torch.zeros(nb._lib.NB_UNIQUE_ID_BYTES, dtype=torch.uint8, device="cuda")
+                if rank == 0:
+                    uid.copy_(torch.from_numpy(nb.World.comm_unique_id()))
+                dist.broadcast(uid, 0)
+                w.comm_init(rank, world, uid.cpu().numpy())
+                mine = torch.from_numpy(w.comm_peer_export()).cuda()
+                blocks = [torch.empty_like(mine) for _ in range(world)]
+                dist.all_gather(blocks, mine)
+                w.comm_peer_import(torch.stack(blocks).cpu().numpy())
+            w.set_particles(shallow)
+            w.step(2)
+            w.set_particles(deep)  # much deeper: the first build's guess fails, steps 1..6 of the batch are redone
+            c = nb.Counting()
+            w.step(6, c)
+            res.append((w.particles, c.interactions))
+            w.close()
+        (q, ni), (r, ni1) = res
+        tot = torch.tensor([float(ni)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot)
+        same = all(np.array_equal(q[k].view(np.uint32), r[k].view(np.uint32)) for k in ("x", "y", "vx", "vy", "weight"))
+        print(f"rank {rank}/{world} fused walk + push tree={tree}: bit-identical to 1 GPU {same}, interactions {int(tot.item())} == {ni1}: "
+              f"{int(tot.item()) == ni1}", flush=True)
+        ok = ok and same and int(tot.item()) == ni1
     flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

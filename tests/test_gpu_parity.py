@@ -371,6 +371,24 @@ def test_top_digit_sort_builds_the_same_tree(sc, n):
     f.close()
 
 
+@pytest.mark.parametrize("levels,widths", [(13, 3), (14, 4), (17, 4), (18, 5), (22, 5)])
+def test_top_digit_sort_every_digit_width(monkeypatch, levels, widths):
+    # plans with several 9-bit digits only appear at particular depths (27 / 35 / 45 key bits): ask for that many levels
+    monkeypatch.setenv("NB_B200_SORT_MIN_LEVELS", str(levels))
+    p = scene("galaxy", 150_001)
+    o = ob.Tree(ob.KIND_PIPE_QUAD, p["x"], p["y"], p["weight"]).export()
+    w = nb.World(len(p))
+    w.set_particles(p)
+    w.build_tree()
+    w.set_particles(p)
+    w.build_tree()
+    info = w.tree_info()
+    assert info.sort_redone == 0 and info.sort_top_digits == widths and info.sort_top_levels >= levels, \
+        (info.sort_top_digits, info.sort_top_levels)
+    assert_tree_equal(w.tree(), o, f"top-digit sort over {levels} levels")
+    w.close()
+
+
 def test_top_digit_sort_falls_back_when_the_guess_is_too_shallow():
     shallow, deep = scene("disc", 20_000), scene("plummer", 150_000)
     w = nb.World(len(deep), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
