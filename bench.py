@@ -167,6 +167,8 @@ def hbm_rooflines(kernel_times, n, n_nodes, hbm_gbs, peak_src):
     device time nb_profile_step measured for each (one step, events behind every kernel, L2 flushed before)."""
     per_body = {  # bytes per body
         "morton_kernel": 20.0,          # x, y read (8) + key (8) + slot index (4) written
+        "morton_repair_kernel": 28.0,   # ... + the key the slot's body had at the previous build (8), sort_repair.cuh
+        "sort_repair_kernel": 20.0,     # key read (8); key + slot written (12)
         "sort_histogram_kernel": 8.0,   # one read of the keys, the digits of the passes that run
         "sort_onesweep_kernel": 24.0,   # (key, slot) read + written
         "tree_count_kernel": 13.0,      # key read (8) + leaf depth (1) + node-count prefix (4) written

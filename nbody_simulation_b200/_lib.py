@@ -79,7 +79,8 @@ class NbTreeInfo(C.Structure):
         ("sort_top_digits", C.c_uint32),
         ("sort_redone", C.c_uint32),
         ("sort_top_levels", C.c_uint32),
-        ("reserved", C.c_uint32 * 2),
+        ("sort_repaired", C.c_uint32),
+        ("sort_movers", C.c_uint32),
     ]
 
 

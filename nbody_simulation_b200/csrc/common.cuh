@@ -45,6 +45,9 @@ struct Meta {
   unsigned long long interactions; // evaluations of calculate_gravity (main.rs:235-253)
   unsigned long long node_tests;   // opening tests (main.rs:370-372)
   const void *node_base;           // TreeArrays::node again, for the traversal to LOAD rather than take as a parameter (traverse.cuh)
+  uint32_t n_movers;        // sort_repair.cuh: bodies whose key left the cell of the sorted depth since the previous build
+  uint32_t n_out;           // ... and bodies outside the root square (both counted by morton_repair_kernel)
+  uint32_t repair_failed;   // != 0: a repair found more movers than it takes (the host backs off to the radix sort)
 };
 
 // Common prefix length of two sorted 48-bit keys, in tree levels of BPL bits each.

@@ -22,6 +22,7 @@
 #include "integrate.cuh"
 #include "morton.cuh"
 #include "radix_sort.cuh"
+#include "sort_repair.cuh"
 #include "scan.cuh"
 #include "traverse.cuh"
 #include "traverse_group.cuh"
@@ -101,6 +102,7 @@ struct nb_ctx {
   BodyArrays body[2]{};
   int cur = 0; // body[cur] holds the current state (slot order)
   unsigned long long *keys[2]{};
+  unsigned long long *keys_new = nullptr; // sort_repair.cuh: this build's keys in slot order, beside the old sorted keys
   uint32_t *vals[2]{};
   int sorted_in = 0; // keys[sorted_in] / vals[sorted_in] hold the sorted keys / tree order
   uint8_t *leafdepth = nullptr;
@@ -144,6 +146,18 @@ struct nb_ctx {
   uint32_t peer_epoch = 0;
   bool aos_fresh = false;         // c->aos holds the uploaded records of the CURRENT state (caller order == slot order)
   uint32_t aos_permute_min = 1u << 21; // bodies from which the first build after an upload re-orders through the AoS copy
+  // sort_repair.cuh: the state is in the order of the tree it was last integrated with, and keys[sorted_in] holds that
+  // tree's sorted keys (sorted on their top keys_sorted_bits bits, keys_sorted_n of them)
+  bool order_coherent = false;
+  int keys_sorted_bits = 0;
+  uint32_t keys_sorted_n = 0;
+  bool movers_valid = false;     // movers_seen is the count of the last build (of this state), read at the last synchronisation
+  uint32_t movers_seen = 0;
+  bool last_counted = false;     // the last build enqueued counted its movers
+  uint32_t repair_off = 0;       // builds to stay away from the repair after one failed
+  bool no_repair = false;        // NB_B200_NO_REPAIR=1
+  bool last_repaired = false, redo_guess_repaired = false, last_failed_repaired = false;
+  RepairScratch repair{};
   int sort_min_levels = 8;        // NB_B200_SORT_MIN_LEVELS: least depth a top-digit sort covers (tests: reach every digit width)
   bool no_fuse = false;           // NB_B200_NO_FUSE=1: keep integrate + push a kernel of its own (A/B runs)
   bool v_partial = false;         // peer exchange: only the velocities of the owned slots are valid here (integrate.cuh)
@@ -332,26 +346,76 @@ int enqueue_build(nb_ctx *c) {
   }
   c->last_top_passes = top_passes;
   c->last_top_levels = sorted_levels;
+  // The state is still in the order of the tree it was integrated with: repair that order instead of sorting
+  // (sort_repair.cuh).  Needs the old keys sorted at least as deep as this build sorts.
+  const bool aligned = top_passes > 0 && c->order_coherent && !c->no_repair && c->repair_off == 0 && c->keys_sorted_n == n &&
+                       c->keys_sorted_bits >= plan.sorted_bits && n >= 4096u && c->h_meta->n_in == n;
+  if (top_passes > 0 && c->order_coherent && c->repair_off) --c->repair_off;
+  // ... and only after a build that counted few enough movers; the others count them in front of their radix sort
+  const bool repair = aligned && c->movers_valid && c->movers_seen <= (uint32_t)kRepairMax / 2u;
+  c->last_counted = aligned;
+  c->order_coherent = false;
+  c->last_repaired = repair;
   c->last_redone = c->redo_next;
   c->last_failed_guess = c->redo_guess;
   c->last_failed_levels = c->redo_guess_levels;
+  c->last_failed_repaired = c->redo_guess_repaired;
   c->redo_next = false;
+  int which;
   { // only the levels the top-digit sort covers (the check in tree_count_kernel catches a deeper leaf)
     const uint32_t mg = cdiv(cdiv(n, 4), 256);
     const int q = c->quad ? 1 : 0;
-#define NB_MORTON(L) morton_kernel<L><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0])
-    if (sorted_levels == 0 || sorted_levels > 20) NB_MORTON(kQuadLevels);
-    else if (sorted_levels <= 8) NB_MORTON(8);
-    else if (sorted_levels <= 10) NB_MORTON(10);
-    else if (sorted_levels <= 12) NB_MORTON(12);
-    else if (sorted_levels <= 13) NB_MORTON(13);
-    else if (sorted_levels <= 14) NB_MORTON(14);
-    else if (sorted_levels <= 16) NB_MORTON(16);
-    else NB_MORTON(20);
+    const int lv = (sorted_levels == 0 || sorted_levels > 20) ? kQuadLevels : sorted_levels <= 8 ? 8 : sorted_levels <= 10 ? 10
+                 : sorted_levels <= 12 ? 12 : sorted_levels <= 13 ? 13 : sorted_levels <= 14 ? 14 : sorted_levels <= 16 ? 16 : 20;
+    if (aligned) {
+      const int p = c->sorted_in, shift = plan.shift[0];
+      const unsigned long long *prev = c->keys[p];
+      unsigned long long *knew = repair ? c->keys_new : c->keys[0];
+      uint32_t *vnew = repair ? nullptr : c->vals[0];
+      NB_CUDA(c, cudaMemsetAsync(&c->meta->n_movers, 0, 2 * sizeof(uint32_t), st)); // n_movers, n_out
+#define NB_MORTON(L) morton_repair_kernel<L><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, prev, c->leafdepth, knew, vnew, c->repair)
+      switch (lv) {
+      case 8: NB_MORTON(8); break;
+      case 10: NB_MORTON(10); break;
+      case 12: NB_MORTON(12); break;
+      case 13: NB_MORTON(13); break;
+      case 14: NB_MORTON(14); break;
+      case 16: NB_MORTON(16); break;
+      case 20: NB_MORTON(20); break;
+      default: NB_MORTON(kQuadLevels); break;
+      }
 #undef NB_MORTON
+      prof_mark(st, "morton_repair_kernel");
+      if (repair) {
+        repair_movers_kernel<<<1, 1024, 0, st>>>(c->meta, n, shift, c->repair, c->step_seq);
+        prof_mark(st, "repair_movers_kernel");
+        sort_repair_kernel<<<cdiv(n, (uint32_t)kRepairTile), kRepairThreads, 0, st>>>(c->meta, n, prev, c->leafdepth, knew, shift, c->repair, c->keys[p ^ 1],
+                                                         c->vals[p ^ 1], c->step_seq);
+        prof_mark(st, "sort_repair_kernel");
+        g_launches += 2;
+        which = p ^ 1;
+      } else {
+        which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, plan, c->sort, st, c->meta);
+      }
+    } else {
+#define NB_MORTON(L) morton_kernel<L><<<mg, 256, 0, st>>>(b0.x, b0.y, c->meta, n, q, c->keys[0], c->vals[0])
+      switch (lv) {
+      case 8: NB_MORTON(8); break;
+      case 10: NB_MORTON(10); break;
+      case 12: NB_MORTON(12); break;
+      case 13: NB_MORTON(13); break;
+      case 14: NB_MORTON(14); break;
+      case 16: NB_MORTON(16); break;
+      case 20: NB_MORTON(20); break;
+      default: NB_MORTON(kQuadLevels); break;
+      }
+#undef NB_MORTON
+      prof_mark(st, "morton_kernel");
+      which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, plan, c->sort, st, c->meta);
+    }
   }
-  prof_mark(st, "morton_kernel");
-  const int which = radix_sort_pairs(c->keys[0], c->vals[0], c->keys[1], c->vals[1], n, plan, c->sort, st, c->meta);
+  c->keys_sorted_bits = plan.sorted_bits;
+  c->keys_sorted_n = n;
   c->sorted_in = which;
   const unsigned long long *skeys = c->keys[which];
   uint32_t *order = c->vals[which];
@@ -554,6 +618,7 @@ int enqueue_integrate(nb_ctx *c, float dt, cudaEvent_t ev_after_integrate, bool 
   NB_CUDA(c, cudaGetLastError());
   c->cur ^= 1;
   c->tree_valid = false;
+  c->order_coherent = c->quad; // the new state is in the order of this step's tree (sort_repair.cuh)
   return NB_OK;
 }
 
@@ -575,6 +640,13 @@ int sync_and_check(nb_ctx *c) {
     c->redo_next = true;
     c->redo_guess = c->last_top_passes;
     c->redo_guess_levels = c->last_top_levels;
+    c->redo_guess_repaired = c->h_meta->repair_failed != 0;
+    c->order_coherent = false; // the failed steps carried the state over: not in the order of the last build's keys
+    c->movers_valid = false; // count again before the next repair
+    if (c->h_meta->repair_failed) { // a burst of movers, a body left the root square, an over-full leaf: radix sort for a while
+      c->repair_off = 256;
+      NB_CUDA(c, cudaMemsetAsync(&c->meta->repair_failed, 0, sizeof(uint32_t), c->stream));
+    }
     ++c->resorts;
     NB_CUDA(c, cudaMemsetAsync(&c->meta->fail_seq, 0xff, sizeof(uint32_t), c->stream));
     NB_CUDA(c, cudaMemsetAsync(&c->meta->error, 0, sizeof(uint32_t), c->stream));
@@ -582,6 +654,10 @@ int sync_and_check(nb_ctx *c) {
   } else if (c->quad && c->n && c->h_meta->n_nodes) { // the mirror describes the last build enqueued
     c->last_max_depth = c->h_meta->max_depth;
     c->depth_known = true;
+    if (c->last_counted) { // sort_repair.cuh: few enough bodies changed cells for the next builds to repair the order?
+      c->movers_seen = c->h_meta->n_movers;
+      c->movers_valid = true;
+    }
   }
   if (c->h_meta->error & 4u) return fail(c, NB_ERR_NCCL, "peer exchange timed out: a rank did not signal its push within 10 s");
   if (c->h_meta->error & 1u) {
@@ -785,7 +861,8 @@ void nb_destroy(nb_ctx *c) {
   free_bodies(c->body[0]);
   free_bodies(c->body[1]);
   for (int i = 0; i < 2; ++i) { cudaFree(c->keys[i]); cudaFree(c->vals[i]); }
-  cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.ghist); cudaFree(c->sort.tickets); cudaFree(c->sort.status); cudaFree(c->sort.bsum);
+  cudaFree(c->keys_new);
+  cudaFree(c->leafdepth); cudaFree(c->nstart); cudaFree(c->sort.ghist); cudaFree(c->sort.tickets); cudaFree(c->repair.mkey); cudaFree(c->repair.mslot); cudaFree(c->repair.s_slot); cudaFree(c->repair.t_sorted); cudaFree(c->repair.k_sorted); cudaFree(c->repair.slot_sorted); cudaFree(c->sort.status); cudaFree(c->sort.bsum);
   cudaFree(c->T.box); cudaFree(c->T.node); cudaFree(c->T.mass); cudaFree(c->T.depth);
   cudaFree(c->T.bmax); cudaFree(c->T.arrive); cudaFree(c->T.kids);
   for (void *p : c->peer_mapped) cudaIpcCloseMemHandle(p);
@@ -844,6 +921,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   c->cfg = *cfg;
   c->device = cfg->device;
   if (const char *e = std::getenv("NB_B200_NO_FUSE")) c->no_fuse = e[0] == '1';
+  if (const char *e = std::getenv("NB_B200_NO_REPAIR")) c->no_repair = e[0] == '1';
   if (const char *e = std::getenv("NB_B200_SORT_MIN_LEVELS")) c->sort_min_levels = std::min(24, std::max(8, std::atoi(e)));
   if (const char *e = std::getenv("NB_B200_AOS_PERMUTE_MIN")) c->aos_permute_min = (uint32_t)std::strtoul(e, nullptr, 10);
   c->quad = cfg->tree_kind == NB_TREE_QUAD;
@@ -867,6 +945,7 @@ nb_ctx *nb_create(const nb_config *cfg) {
   for (int i = 0; i < 2; ++i) {
     if (alloc_bodies(c, c->body[i], na) != NB_OK) { g_create_error = c->err; nb_destroy(c); return nullptr; }
     NB_TRY(dmalloc(&c->keys[i], na));
+    if (i == 0) NB_TRY(dmalloc(&c->keys_new, na));
     NB_TRY(dmalloc(&c->vals[i], na));
   }
   NB_TRY(dmalloc(&c->leafdepth, na));
@@ -874,6 +953,12 @@ nb_ctx *nb_create(const nb_config *cfg) {
   c->sort.status_words = sort_status_words((uint32_t)na);
   NB_TRY(dmalloc(&c->sort.ghist, (size_t)8192));
   NB_TRY(dmalloc(&c->sort.tickets, (size_t)16));
+  NB_TRY(dmalloc(&c->repair.mkey, (size_t)kRepairMax));
+  NB_TRY(dmalloc(&c->repair.mslot, (size_t)kRepairMax));
+  NB_TRY(dmalloc(&c->repair.s_slot, (size_t)kRepairMax));
+  NB_TRY(dmalloc(&c->repair.t_sorted, (size_t)kRepairMax));
+  NB_TRY(dmalloc(&c->repair.k_sorted, (size_t)kRepairMax));
+  NB_TRY(dmalloc(&c->repair.slot_sorted, (size_t)kRepairMax));
   NB_TRY(dmalloc(&c->sort.status, c->sort.status_words));
   NB_TRY(dmalloc(&c->sort.bsum, na / 256 + na / 262144 + 64)); // block totals of tree_count_kernel (256 bodies) / of the flag scan
   const size_t ncap = 2 * na + 65536;
@@ -1008,6 +1093,8 @@ int nb_set_bodies_aos(nb_ctx *c, const nb_particle *bodies, size_t n) {
   c->v_partial = false;
   c->aos_fresh = false;
   c->tree_valid = false;
+  c->order_coherent = false;
+  c->movers_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
   aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
@@ -1026,6 +1113,8 @@ int nb_set_bodies_soa(nb_ctx *c, const float *x, const float *y, const float *vx
   c->v_partial = false;
   c->aos_fresh = false;
   c->tree_valid = false;
+  c->order_coherent = false;
+  c->movers_valid = false;
   if (n == 0) return NB_OK;
   BodyArrays &b = c->body[c->cur];
   NB_CUDA(c, cudaMemcpyAsync(b.x, x, n * 4, cudaMemcpyHostToDevice, c->stream));
@@ -1078,6 +1167,8 @@ int nb_scene_generate_device(nb_ctx *c, int32_t scene, uint64_t seed, size_t n) 
     return fail(c, NB_ERR_INVALID, "nb_scene_generate_device: unknown scene");
   NB_CUDA(c, cudaSetDevice(c->device));
   c->tree_valid = false;
+  c->order_coherent = false;
+  c->movers_valid = false;
   c->v_partial = false;
   c->aos_fresh = false; // the staging buffer no longer describes the state
   cudaStream_t st = c->stream;
@@ -1188,6 +1279,8 @@ int nb_world_update(nb_ctx *c, nb_particle *bodies, size_t n, float delta, nb_co
   c->v_partial = false;
   c->aos_fresh = false;
   c->tree_valid = false;
+  c->order_coherent = false;
+  c->movers_valid = false;
   if (n == 0) return NB_OK;
   NB_CUDA(c, cudaMemcpyAsync(c->aos, bodies, n * sizeof(nb_particle), cudaMemcpyHostToDevice, c->stream));
   aos_to_soa_kernel<<<cdiv((uint32_t)n, 256), 256, 0, c->stream>>>(c->aos, c->body[c->cur], (uint32_t)n);
@@ -1218,6 +1311,8 @@ int nb_world_update_shard(nb_ctx *c, nb_particle *slice, size_t first, size_t co
   c->v_partial = false;
   c->aos_fresh = false;
   c->tree_valid = false;
+  c->order_coherent = false;
+  c->movers_valid = false;
   if (n_total == 0) return NB_OK;
   cudaStream_t st = c->stream;
   auto handshake = [&]() {
@@ -1404,6 +1499,8 @@ int nb_get_tree_info(nb_ctx *c, nb_tree_info *info) {
   info->root_x0 = m.x0; info->root_y0 = m.y0; info->root_h = m.h;
   info->sort_top_digits = c->n ? (uint32_t)(c->last_redone ? c->last_failed_guess : c->last_top_passes) : 0;
   info->sort_top_levels = c->n ? (uint32_t)(c->last_redone ? c->last_failed_levels : c->last_top_levels) : 0;
+  info->sort_repaired = c->n ? (uint32_t)(c->last_redone ? c->last_failed_repaired : c->last_repaired) : 0;
+  info->sort_movers = info->sort_repaired && !c->last_redone ? c->h_meta->n_movers : 0;
   info->sort_redone = (c->n && c->last_redone) ? 1u : 0u;
   return NB_OK;
 }

@@ -15,5 +15,6 @@ for _ in range(5):
     t = w.profile_step()
     if best is None or sum(u for _, u in t) < sum(u for _, u in best):
         best = t
+w.build_tree(); ti = w.tree_info(); print("repaired", ti.sort_repaired, "movers", ti.sort_movers, "n_in", ti.n_in_tree, end=" | ")
 print(n, " ".join(f"{k.split('_kernel')[0]}={u:.1f}" for k, u in best), "| build", round(sum(u for k, u in best if not k.startswith(("traverse", "integrate"))), 1))
 w.close()

@@ -38,7 +38,7 @@ def test_abi_version_and_struct_sizes():
     # fields carved out of the reserved words (ABI version unchanged: old callers passed / read zeros there)
     assert _lib.NbConfig.full_sort.offset == 52 and _lib.NbConfig.fast_walk_group.offset == 56 and _lib.NbConfig.reserved.offset == 60
     assert _lib.NbTreeInfo.sort_top_digits.offset == 52 and _lib.NbTreeInfo.sort_redone.offset == 56
-    assert _lib.NbTreeInfo.sort_top_levels.offset == 60 and _lib.NbTreeInfo.reserved.offset == 64
+    assert _lib.NbTreeInfo.sort_top_levels.offset == 60 and _lib.NbTreeInfo.sort_repaired.offset == 64 and _lib.NbTreeInfo.sort_movers.offset == 68
     cfg = _lib.NbConfig()
     L.nb_default_config(C.byref(cfg), 10)
     assert cfg.full_sort == 0 and not any(cfg.reserved)

@@ -389,6 +389,110 @@ def test_top_digit_sort_every_digit_width(monkeypatch, levels, widths):
     w.close()
 
 
+# ---- repairing the previous order instead of sorting: sort_repair.cuh ------------------------------------------
+def _moving(name, n, movers_per_step, seed=5):
+    """A scene whose bodies drift in random directions, fast enough for roughly `movers_per_step` of them to leave the
+    cell of their leaf in a step of dt = 0.1 (0: at rest) — fewer in fact: the estimate takes every leaf to be as small
+    as the deepest ones."""
+    p = scene(name, n)
+    w = nb.World(len(p))
+    w.set_particles(p)
+    w.build_tree()
+    info = w.tree_info()
+    w.close()
+    cell = info.root_h / 2.0 ** info.max_depth
+    speed = movers_per_step / (1.27 * len(p)) * cell / 0.1  # a body moving d crosses a cell line with p = 1.27 d / cell
+    rng = np.random.default_rng(seed)
+    ang = rng.uniform(0, 2 * np.pi, len(p))
+    p["vx"] = (speed * np.cos(ang)).astype(np.float32)
+    p["vy"] = (speed * np.sin(ang)).astype(np.float32)
+    return p
+
+
+@pytest.mark.parametrize("sc,n,movers", [("disc", 200_000, 0), ("galaxy", 150_001, 900), ("disc", 300_000, 1500),
+                                         ("disc", 5_000, 300)])
+def test_sort_repair_builds_the_same_tree(monkeypatch, sc, n, movers):
+    # a build whose state is still in the previous tree's order counts the bodies that left their cell; once that count
+    # is small the builds stop sorting and only re-insert those bodies.  Tree and trajectory stay bit-identical to the
+    # oracle's / to a context that always sorts
+    p = _moving(sc, n, movers)
+    w = nb.World(len(p), theta=0.5, dt=0.1, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    w.step(1)          # full sort (no depth known)
+    w.step(2)          # top-digit sorts that count the movers
+    w.step(2)          # repairs
+    w.build_tree()
+    info = w.tree_info()
+    assert info.sort_redone == 0 and info.sort_top_digits > 0
+    assert info.sort_repaired == 1, ("the build after a step must repair the order", info.sort_movers, info.n_in_tree, info.n_bodies, info.overflow_leaves)
+    if movers == 0:
+        assert info.sort_movers <= 20, info.sort_movers
+    else:
+        assert 0 < info.sort_movers <= 2048, info.sort_movers
+    q = w.particles
+    o = ob.Tree(ob.KIND_PIPE_QUAD, q["x"], q["y"], q["weight"]).export()
+    assert_tree_equal(w.tree(), o, f"{sc}/repaired order, {info.sort_movers} movers")
+    monkeypatch.setenv("NB_B200_NO_REPAIR", "1")
+    ref = nb.World(len(p), theta=0.5, dt=0.1, force_mode=nb.NB_FORCE_EXACT)
+    ref.set_particles(p)
+    ref.step(1)
+    ref.step(4)
+    ref.build_tree()
+    assert ref.tree_info().sort_repaired == 0
+    assert np.array_equal(bits(q), bits(ref.particles))
+    c, cr = nb.Counting(), nb.Counting()
+    w.step(5, c)
+    ref.step(5, cr)
+    assert c.interactions == cr.interactions and c.node_tests == cr.node_tests
+    assert np.array_equal(bits(w.particles), bits(ref.particles))
+    w.close()
+    ref.close()
+
+
+def test_sort_repair_gives_up_when_too_many_bodies_moved(monkeypatch):
+    # the movers were few when counted, then a burst of them: more than a repair takes.  The step is redone with the
+    # radix sort (inside a batch of steps) and the trajectory is that of a context that always sorts; a scene that
+    # moves a lot from the start never tries
+    p = _moving("disc", 100_000, 600)
+    w = nb.World(len(p), theta=0.5, dt=0.1, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    w.step(1)
+    w.step(2)
+    fast = w.particles
+    fast["vx"] *= 200.0
+    fast["vy"] *= 200.0
+    ref_start = fast.copy()
+    w.set_particles(fast)  # an upload: in caller order, so no repair until the order is the tree's again
+    w.step(1)
+    w.step(1)
+    w.build_tree()
+    info = w.tree_info()
+    assert info.sort_repaired == 0 and info.sort_redone == 0  # counted ~40 000 movers: stays with the radix sort
+    w.close()
+    # the burst itself: slow bodies, repairs running, then the velocities jump on the device side of a batch?  There
+    # is no such call — so shrink the cells instead: a context whose repair limit is hit because dt grows
+    w = nb.World(len(p), theta=0.5, dt=0.1, force_mode=nb.NB_FORCE_EXACT)
+    w.set_particles(p)
+    w.step(1)
+    w.step(2)          # counted ~200 movers
+    w.set_params(0.5, 40.0, nb.NB_FORCE_EXACT)  # dt x400: ~80 000 movers in the next step
+    c = nb.Counting()
+    w.step(4, c)       # the first repair fails; the batch is redone with the radix sort
+    assert c.steps == 4
+    monkeypatch.setenv("NB_B200_NO_REPAIR", "1")
+    ref = nb.World(len(p), theta=0.5, dt=0.1, force_mode=nb.NB_FORCE_EXACT)
+    ref.set_particles(p)
+    ref.step(1)
+    ref.step(2)
+    ref.set_params(0.5, 40.0, nb.NB_FORCE_EXACT)
+    cr = nb.Counting()
+    ref.step(4, cr)
+    assert c.interactions == cr.interactions
+    assert np.array_equal(bits(w.particles), bits(ref.particles))
+    w.close()
+    ref.close()
+
+
 def test_top_digit_sort_falls_back_when_the_guess_is_too_shallow():
     shallow, deep = scene("disc", 20_000), scene("plummer", 150_000)
     w = nb.World(len(deep), theta=0.5, force_mode=nb.NB_FORCE_EXACT)
