@@ -365,6 +365,10 @@ def main():
     for _ in range(args.steps):
         if not args.no_flush:
             w.flush_l2()
+        if dist is not None:
+            # every rank starts the step together: the ranks hand-shake at the END of a step, so a rank whose host was
+            # quicker through the flush would count its wait for the slowest starter as device time of the step
+            barrier()
         w.step(1, c)
     barrier()
     wall = time.perf_counter() - t0
@@ -466,6 +470,8 @@ def main():
         w.set_counting(False)
         w.set_particles(parts)
         w.step(warm)
+        w.step(1)  # the depth is known: top-digit sort, movers counted
+        w.step(1)  # ... and the builds the timed steps run (order repair when few bodies left their leaf cell)
         w.flush_l2()
         kernel_times = w.profile_step()
     # what the builds of the timed steps sorted (one more build of the final state, outside every timed region)
@@ -474,7 +480,10 @@ def main():
     sort_note = ("n/a" if args.tree == "bvhref" else "every key digit" if ti.sort_top_digits == 0 else
                  f"{ti.sort_top_digits} passes over the top {ti.sort_top_levels} quadtree levels of the keys per build (a full sort takes 6), the depth guess checked on the device in every step "
                  f"and redone in full when too shallow (last build redone: {bool(ti.sort_redone)}); same tree bit for bit "
-                 "as the full sort (tests/test_gpu_parity.py::test_top_digit_sort_*), --full-sort turns it off")
+                 "as the full sort (tests/test_gpu_parity.py::test_top_digit_sort_*), --full-sort turns it off; a build whose "
+                 "state is still in the previous tree's order re-inserts the bodies that left their leaf cell instead of "
+                 f"sorting while those are few (csrc/sort_repair.cuh; last build: repaired={bool(ti.sort_repaired)}, "
+                 f"{int(ti.sort_movers)} movers; NB_B200_NO_REPAIR=1 turns it off)")
     if clocks is not None:
         clocks["window"] = "counter replay, warm-up, timed steps and e2e steps (nvidia-smi -lms 10, median)"
     if rank == 0:
@@ -499,7 +508,8 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, n_total),
             "details": {"force_mode": args.force, "parallelism": f"morton-range x{world}" + (f", exchange={args.exchange}" if world > 1 else ""),
-                        "l2": "not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps",
+                        "l2": ("not flushed" if args.no_flush else "256 MB scratch overwritten between timed steps") +
+                              (" (N > 1: then a barrier, so that every rank starts the step together)" if world > 1 else ""),
                         "interaction_count": "from an identical replay of the timed steps with counters on",
                         "sort": sort_note, "tree_depth": int(ti.max_depth), "n_nodes": int(ti.n_nodes)},
             "steps_per_s": args.steps / dev_s,

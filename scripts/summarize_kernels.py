@@ -21,7 +21,7 @@ for row in csv.DictReader(lines):
     u = row["Metric Unit"]
     v *= {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1, "ns": 1, "us": 1e3, "ms": 1e6}.get(u, 1)
     agg.setdefault(k, collections.defaultdict(list))[row["Metric Name"]].append(v)
-alg = {"morton_kernel": 20 * n, "morton_hist_kernel": 20 * n, "sort_histogram_kernel": 8 * n, "sort_onesweep_kernel": 24 * n, "tree_count_kernel": 13 * n,
+alg = {"morton_repair_kernel": 29 * n, "sort_repair_kernel": 21 * n, "morton_kernel": 20 * n, "morton_hist_kernel": 20 * n, "sort_histogram_kernel": 8 * n, "sort_onesweep_kernel": 24 * n, "tree_count_kernel": 13 * n,
        "tree_emit_quad_kernel": 84 * nn, "tree_link_kernel": 56 * nn, "tree_finish_kernel": 40 * n + 100 * nn,
        "integrate_resort_kernel": 60 * n}
 with open(os.path.join(ROOT, "profiles", f"{tag}_kernels.md"), "w") as f:
