@@ -349,7 +349,8 @@ int enqueue_build(nb_ctx *c) {
   // The state is still in the order of the tree it was integrated with: repair that order instead of sorting
   // (sort_repair.cuh).  Needs the old keys sorted at least as deep as this build sorts.
   const bool aligned = top_passes > 0 && c->order_coherent && !c->no_repair && c->repair_off == 0 && c->keys_sorted_n == n &&
-                       c->keys_sorted_bits >= plan.sorted_bits && n >= 4096u && c->h_meta->n_in == n;
+                       c->keys_sorted_bits >= plan.sorted_bits && n >= 4096u && c->h_meta->n_in == n &&
+                       c->leaf_cap < kRepairLeafScan && c->h_meta->overflow_leaves == 0; // leaves it can rank in place
   if (top_passes > 0 && c->order_coherent && c->repair_off) --c->repair_off;
   // ... and only after a build that counted few enough movers; the others count them in front of their radix sort
   const bool repair = aligned && c->movers_valid && c->movers_seen <= (uint32_t)kRepairMax / 2u;

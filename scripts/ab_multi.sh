@@ -1,4 +1,6 @@
-# gpurun --gpus N -- 'bash scripts/_multi_ab.sh N'
+# N-GPU pass: tests/multi_gpu_check.py (bit-identity with one GPU, both exchanges, sharded call, fused walk + push,
+# a failed depth guess inside a batch), then the bench line with and without the fused kernel / second stream.
+#   gpurun --gpus N -- 'bash scripts/ab_multi.sh N'
 cd $GRAFT_REPO_ROOT
 N=${1:-2}
 mkdir -p gpurun_out

@@ -1,3 +1,4 @@
+# The driver's N-GPU bench command, with a one-line summary.   gpurun --gpus N -- 'bash scripts/bench_multi.sh N'
 cd $GRAFT_REPO_ROOT
 N=${1:-8}
 mkdir -p gpurun_out

@@ -1,3 +1,5 @@
+"""How many bodies leave their leaf cell per step (sort_repair.cuh) and whether the builds repair or sort:
+  python scripts/movers_per_step.py 8000000 disc"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import nbody_simulation_b200 as nb
