@@ -155,6 +155,7 @@ struct nb_ctx {
   uint32_t movers_seen = 0;
   bool last_counted = false;     // the last build enqueued counted its movers
   uint32_t repair_off = 0;       // builds to stay away from the repair after one failed
+  uint32_t batch_steps = 1;      // steps the current do_steps batch enqueues before the host looks again
   bool no_repair = false;        // NB_B200_NO_REPAIR=1
   bool last_repaired = false, redo_guess_repaired = false, last_failed_repaired = false;
   RepairScratch repair{};
@@ -353,7 +354,8 @@ int enqueue_build(nb_ctx *c) {
                        c->leaf_cap < kRepairLeafScan && c->h_meta->overflow_leaves == 0; // leaves it can rank in place
   if (top_passes > 0 && c->order_coherent && c->repair_off) --c->repair_off;
   // ... and only after a build that counted few enough movers; the others count them in front of their radix sort
-  const bool repair = aligned && c->movers_valid && c->movers_seen <= (uint32_t)kRepairMax / 2u;
+  // (a batch of steps enqueued blind cannot react to a count that grows: stay further below the limit there)
+  const bool repair = aligned && c->movers_valid && c->movers_seen <= (uint32_t)kRepairMax / (c->batch_steps > 8u ? 8u : 2u);
   c->last_counted = aligned;
   c->order_coherent = false;
   c->last_repaired = repair;
@@ -716,6 +718,7 @@ int do_steps(nb_ctx *c, uint32_t n_steps, float dt, nb_counting *out) {
     // enqueue a batch blind (no host synchronisation inside a step), then look once
     const uint32_t batch = std::min(remaining, 256u); // bounds the number of live events
     const uint32_t seq0 = c->step_seq;
+    c->batch_steps = batch;
     for (uint32_t s = 0; s < batch; ++s) {
       cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, e3 = nullptr, e4 = nullptr;
       if (out) {
@@ -1375,6 +1378,7 @@ int nb_build_tree(nb_ctx *c, nb_counting *out) {
       if (!e1) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
       NB_CUDA(c, cudaEventRecord(e0, c->stream));
     }
+    c->batch_steps = 1;
     rc = enqueue_build(c);
     if (rc != NB_OK) return rc;
     if (out) NB_CUDA(c, cudaEventRecord(e1, c->stream));
@@ -1398,6 +1402,7 @@ int nb_accel(nb_ctx *c, float *ax, float *ay, nb_counting *out) {
     cudaEvent_t e0 = next_event(c), e1 = next_event(c), e2 = next_event(c);
     if (!e2) return fail(c, NB_ERR_CUDA, "cudaEventCreate failed");
     NB_CUDA(c, cudaEventRecord(e0, c->stream));
+    c->batch_steps = 1;
     if (!c->tree_valid && (rc = enqueue_build(c)) != NB_OK) return rc;
     NB_CUDA(c, cudaEventRecord(e1, c->stream));
     if ((rc = enqueue_traverse(c, 0, c->n)) != NB_OK) return rc;
