@@ -63,12 +63,11 @@ __global__ void __launch_bounds__(256) morton_repair_kernel(const float *__restr
                                                             const uint8_t *__restrict__ ldepth,
                                                             unsigned long long *keys, uint32_t *vals, RepairScratch R) {
   const float x0 = meta->x0, y0 = meta->y0, h = meta->h;
-  const uint32_t i4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
-  if (i4 >= n) return;
+  const uint32_t i4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u; // (no early exit: the warp counts its movers together)
   float px[4], py[4];
   unsigned long long pk[4];
   uint32_t pl[4];
-  const bool full = i4 + 3 < n;
+  const bool full = i4 + 3 < n && i4 + 3 >= i4;
   if (full) {
     const float4 vx = *reinterpret_cast<const float4 *>(x + i4);
     const float4 vy = *reinterpret_cast<const float4 *>(y + i4);
@@ -81,7 +80,7 @@ __global__ void __launch_bounds__(256) morton_repair_kernel(const float *__restr
   } else {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const bool ok = i4 + k < n;
+      const bool ok = i4 < n && i4 + k < n;
       px[k] = ok ? x[i4 + k] : 0.f;
       py[k] = ok ? y[i4 + k] : 0.f;
       pk[k] = ok ? prev[i4 + k] : 0ull;
@@ -89,19 +88,45 @@ __global__ void __launch_bounds__(256) morton_repair_kernel(const float *__restr
     }
   }
   unsigned long long kk[4];
+  bool mv[4];
+  uint32_t mine = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     kk[k] = morton_chain<LEVELS>(px[k], py[k], x0, y0, h);
     if (!in_domain(px[k], py[k], x0, y0, h)) kk[k] = kKeyOut;
-    if (i4 + k < n) {
-      if (kk[k] == kKeyOut) atomicAdd(&meta->n_out, 1u);
-      const int sh = rp_shift(pl[k]);
-      if ((kk[k] >> sh) != (pk[k] >> sh)) { // rare: no aggregation needed
-        const uint32_t p = atomicAdd(&meta->n_movers, 1u);
+    const bool ok = i4 < n && i4 + k < n;
+    // (a body outside the root square makes the repair give up; a handful is all anybody needs to know about)
+    if (ok && kk[k] == kKeyOut && *reinterpret_cast<volatile uint32_t *>(&meta->n_out) < 64u) atomicAdd(&meta->n_out, 1u);
+    const int sh = rp_shift(pl[k]);
+    mv[k] = ok && (kk[k] >> sh) != (pk[k] >> sh);
+    mine += mv[k] ? 1u : 0u;
+  }
+  // One atomic per warp that has movers, and none once the count is past what a repair takes: a scene in which every
+  // body changes its cell every step (the two-galaxy scene) must not queue a million atomics on one word.
+  const unsigned lane = threadIdx.x & 31;
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= (unsigned)o) inc += v;
+  }
+  const uint32_t wtot = __shfl_sync(0xffffffffu, inc, 31);
+  if (wtot != 0u) {
+    uint32_t base = 0;
+    if (lane == 31) {
+      const uint32_t seen = *reinterpret_cast<volatile uint32_t *>(&meta->n_movers);
+      base = seen > (uint32_t)kRepairMax ? seen : atomicAdd(&meta->n_movers, wtot);
+    }
+    base = __shfl_sync(0xffffffffu, base, 31);
+    uint32_t p = base + inc - mine;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (mv[k]) {
         if (p < (uint32_t)kRepairMax) {
           R.mkey[p] = kk[k];
           R.mslot[p] = i4 + k;
         }
+        ++p;
       }
     }
   }
@@ -109,7 +134,7 @@ __global__ void __launch_bounds__(256) morton_repair_kernel(const float *__restr
     reinterpret_cast<ulonglong2 *>(keys + i4)[0] = make_ulonglong2(kk[0], kk[1]);
     reinterpret_cast<ulonglong2 *>(keys + i4)[1] = make_ulonglong2(kk[2], kk[3]);
     if (vals) *reinterpret_cast<uint4 *>(vals + i4) = make_uint4(i4, i4 + 1, i4 + 2, i4 + 3);
-  } else {
+  } else if (i4 < n) {
     for (int k = 0; k < 4 && i4 + k < n; ++k) {
       keys[i4 + k] = kk[k];
       if (vals) vals[i4 + k] = i4 + k;
